@@ -1,0 +1,155 @@
+// gzb_common.cuh -- constants, device records and small helpers shared by the kernels.
+//
+// Data layout in HBM (per sub-batch of chunks; see DESIGN.md "Data layout"):
+//   in          caller's input, untouched; chunk c = in[c*CHUNK, (c+1)*CHUNK), its dictionary is the
+//               32 KiB before it (no copy: the reference memcpy's it, src/parallel.c:767-774)
+//   tokens      u32[nchunks][CHUNK]      LZ77 token stream of each chunk (k_lz77 -> k_pack)
+//   blocks      BlockRec[nchunks][BPC]   per deflate block: histograms (k_lz77), code tables + header
+//                                        (k_huffman), absolute output bit offset (k_layout)
+//   chunks      ChunkRec[nchunks]        per chunk: CRC-32, fragment size and byte offset
+//   out         caller's output; k_pack writes every block at its final bit position
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace gzb {
+
+constexpr int      MAX_CHUNK   = 131072;          // IN_BUF_SIZE, src/parallel.c:13
+constexpr int      DICT        = 32768;           // DICTIONARY_SIZE, src/parallel.c:15
+constexpr int      TILE        = 2048;            // positions per pipeline step of k_lz77
+constexpr int      RING        = 65536;           // bytes of window kept in shared memory
+constexpr int      LINK_RING   = 32768 + 2 * TILE;// chain links kept in shared memory
+constexpr int      MAXD        = 32768;           // farthest match (deflate's limit)
+constexpr int      TOO_FAR     = 4096;            // lib/zlib/deflate.c:110-112
+constexpr int      HBITS       = 14;              // buckets of the 4-byte chain table
+constexpr int      H3BITS      = 12;              // buckets of the 3-byte single-entry table
+constexpr int      BLOCK_SPAN  = 65536;           // input bytes per deflate block
+constexpr int      MAX_BPC     = MAX_CHUNK / BLOCK_SPAN;   // blocks per chunk
+constexpr int      LZ_THREADS  = 1024;
+constexpr int      NLSYM       = 286;
+constexpr int      NDSYM       = 30;
+constexpr int      HDR_BYTES   = 608;             // worst case 14 + 57 + 316*14 bits = 4495 bits
+
+// Search effort per level.  good/lazy/nice are the reference's configuration_table
+// (lib/zlib/deflate.c:134-146); depth replaces max_chain (DESIGN.md "Level semantics").
+struct LevelParams {
+    int depth, nice, max_lazy, lazy_parse, use_h3;
+};
+
+// One deflate block.  Written by k_lz77 (histograms, token range, input range),
+// k_huffman (plan) and k_layout (out_bit, bfinal).
+struct BlockRec {
+    uint32_t lfreq[288];      // literal/length histogram (_tr_tally, lib/zlib/deflate.h:326-342)
+    uint32_t dfreq[32];       // distance histogram
+    uint16_t lcode[288];      // bit-reversed canonical codes (gen_codes, trees.c:572-605)
+    uint16_t dcode[32];
+    uint8_t  llen[288];
+    uint8_t  dlen[32];
+    uint8_t  header[HDR_BYTES];   // HLIT,HDIST,HCLEN + code-length section (send_all_trees, trees.c:834-858)
+    uint32_t header_bits;
+    uint32_t type;            // 0 stored, 1 static, 2 dynamic (trees.c:962-993)
+    uint32_t tok_begin;       // index into the chunk's token array
+    uint32_t tok_count;
+    uint32_t in_off;          // first input byte covered, relative to the chunk
+    uint32_t in_bytes;        // input bytes covered
+    uint32_t bfinal;
+    uint32_t pad0;
+    uint64_t body_bits;       // size of the chosen encoding in bits, 3 type bits excluded (stored: see k_layout)
+    uint64_t out_bit;         // absolute bit position of the block in the output buffer
+};
+
+struct ChunkRec {
+    uint32_t crc;             // CRC-32 of the chunk's bytes
+    uint32_t n_bytes;         // input bytes in the chunk
+    uint32_t n_blocks;
+    uint32_t n_tokens;
+    uint64_t frag_bytes;      // size of the byte-aligned raw-deflate fragment
+    uint64_t out_byte;        // absolute byte offset of the fragment in the output buffer
+    uint32_t tail_kind;       // 0 none, 1 empty stored block appended for byte alignment
+    uint32_t pad0;
+    uint64_t tail_bit;        // where the alignment block goes
+};
+
+// Running state carried across sub-batches on the device (no host sync in between).
+struct Cursor {
+    uint64_t out_bytes;       // bytes produced so far
+    uint64_t in_bytes;        // bytes consumed so far
+    uint32_t crc;             // CRC-32 of everything consumed so far
+    uint32_t n_chunks;
+    uint32_t n_blocks;
+    int32_t  status;
+};
+
+// ---- token format: bit31 = match; match: (len-3) << 16 | (dist-1); literal: byte ----
+__host__ __device__ __forceinline__ uint32_t tok_match(uint32_t len, uint32_t dist) { return 0x80000000u | ((len - 3u) << 16) | (dist - 1u); }
+
+// ---- deflate symbol maps (RFC 1951 3.2.5; cf. _length_code/_dist_code, lib/zlib/trees.h) ----
+__host__ __device__ __forceinline__ uint32_t len_code(uint32_t len)     // 3..258 -> 0..28
+{
+    uint32_t l = len - 3u;
+    if (l < 8u) return l;
+    if (len == 258u) return 28u;
+#ifdef __CUDA_ARCH__
+    uint32_t n = 31u - __clz(l);
+#else
+    uint32_t n = 31u - (uint32_t)__builtin_clz(l);
+#endif
+    return 4u * (n - 1u) + ((l >> (n - 2u)) & 3u);
+}
+__host__ __device__ __forceinline__ uint32_t len_extra_bits(uint32_t code) { return (code < 8u || code == 28u) ? 0u : (code - 4u) >> 2; }
+__host__ __device__ __forceinline__ uint32_t len_base(uint32_t code)
+{
+    if (code < 8u) return code + 3u;
+    if (code == 28u) return 258u;
+    uint32_t e = (code - 4u) >> 2;
+    return 3u + ((4u + (code & 3u)) << e);
+}
+__host__ __device__ __forceinline__ uint32_t dist_code(uint32_t dist)   // 1..32768 -> 0..29
+{
+    uint32_t d = dist - 1u;
+    if (d < 4u) return d;
+#ifdef __CUDA_ARCH__
+    uint32_t n = 31u - __clz(d);
+#else
+    uint32_t n = 31u - (uint32_t)__builtin_clz(d);
+#endif
+    return 2u * n + ((d >> (n - 1u)) & 1u);
+}
+__host__ __device__ __forceinline__ uint32_t dist_extra_bits(uint32_t code) { return code < 4u ? 0u : (code >> 1) - 1u; }
+__host__ __device__ __forceinline__ uint32_t dist_base(uint32_t code)
+{
+    if (code < 4u) return code + 1u;
+    uint32_t e = (code >> 1) - 1u;
+    return 1u + ((2u + (code & 1u)) << e);
+}
+
+__host__ __device__ __forceinline__ uint32_t hash4(uint32_t v) { return (v * 0x9E3779B1u) >> (32 - HBITS); }
+__host__ __device__ __forceinline__ uint32_t hash3(uint32_t v) { return ((v << 8) * 0x9E3779B1u) >> (32 - H3BITS); }
+
+// CRC-32 (reflected, poly 0xEDB88320) helpers shared by k_crc32 and k_layout.
+constexpr uint32_t CRC_POLY = 0xEDB88320u;
+// a(x) * b(x) mod P in the reflected domain (bit 31 = x^0)
+__host__ __device__ __forceinline__ uint32_t gf2_mul(uint32_t a, uint32_t b)
+{
+    uint32_t p = 0;
+#pragma unroll 1
+    for (int i = 0; i < 32; i++) {
+        if (a & 0x80000000u) p ^= b;
+        a <<= 1;
+        b = (b >> 1) ^ ((b & 1u) ? CRC_POLY : 0u);
+    }
+    return p;
+}
+
+// launchers (defined in the k_*.cu files)
+struct CrcTables;
+void launch_crc32(const uint8_t* in, uint64_t n_bytes, uint32_t chunk, uint32_t nchunks, ChunkRec* chunks, cudaStream_t st);
+void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
+                 uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st);
+void launch_huffman(BlockRec* blocks, const ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, cudaStream_t st);
+void launch_layout(BlockRec* blocks, ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, uint32_t chunk, int final, Cursor* cur, cudaStream_t st);
+void launch_pack(const uint8_t* in, uint32_t chunk, const uint32_t* tokens, const BlockRec* blocks, const ChunkRec* chunks,
+                 uint32_t nchunks, uint32_t bpc, uint8_t* out, cudaStream_t st);
+cudaError_t lz77_configure();
+
+}  // namespace gzb

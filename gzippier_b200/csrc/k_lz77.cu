@@ -1,0 +1,394 @@
+// k_lz77.cu -- LZ77 match finding + greedy/lazy parse + literal/length/distance histograms.
+//
+// Replaces, for one chunk per CTA: deflateSetDictionary (lib/zlib/deflate.c:376-442),
+// INSERT_STRING (:182-185), longest_match (:1236-1377), deflate_fast (:1824-1918),
+// deflate_slow (:1926-2049) and _tr_tally (deflate.h:326-342).  Not a port: zlib walks one
+// position at a time and skips positions inside matches; here EVERY position of a 2 KiB tile is
+// searched in parallel (one thread per position) against hash chains that an "inserter" warp
+// builds in exact stream order one tile ahead, and the greedy/lazy parse is then a pure
+// function next(p) of the per-position results, evaluated by a speculative parallel walk.
+//
+// One persistent CTA (1024 threads, ~200 KB shared memory) per SM, chunks handed out by an
+// atomic counter.  Shared memory holds the whole search state of the chunk:
+//   ring   64 KiB  window bytes, stream position & 0xFFFF  (dictionary + chunk stream)
+//   link   72 KiB  u16 delta to the previous position in the same 4-byte bucket (0 = none),
+//                  indexed by stream position mod LINK_RING; deltas need no sliding
+//   head   32 KiB  u16 last position (mod 64 Ki) per 4-byte bucket -- inserter-private
+//   head3   8 KiB  u16 last position per 3-byte bucket (single entry, no chain)
+//   c3      8 KiB  per-position delta to the most recent 3-byte twin, double-buffered per tile
+//   mlen/mdist 12 KiB  per-position best match of the last two tiles
+// Stale/aliased head entries are detected by re-hashing the bytes at the candidate, which makes
+// the chains exactly "all earlier positions of the same bucket, most recent first"
+// (oracle/engine_model.c is the sequential statement of the same semantics).
+#include "gzb_common.cuh"
+
+namespace gzb {
+
+namespace {
+
+constexpr uint32_t FULL = 0xFFFFFFFFu;
+constexpr int NWARPS = LZ_THREADS / 32;
+constexpr int GROUPS_PER_TILE = TILE / 32;
+constexpr int MRING = 2 * TILE;           // per-position match results kept for two tiles
+
+struct Smem {
+    uint32_t ring32[RING / 4];
+    uint16_t link[LINK_RING];
+    uint16_t head[1 << HBITS];
+    uint16_t head3[1 << H3BITS];
+    uint16_t c3[2][TILE];
+    uint16_t mdist[MRING];                // dist-1, 0xFFFF = no match
+    uint8_t  mlen[MRING];                 // len-3
+    uint32_t lfreq[288];
+    uint32_t dfreq[32];
+    unsigned long long masks[32];         // token-start bitmap of the tile being parsed
+    uint32_t seg_prefix[33];
+    uint32_t grp_ctr[2];                  // dynamic group scheduler, alternating per pipeline step
+    uint32_t chunk_idx;
+    uint32_t entry;                       // next token start (stream position)
+    uint32_t ntok;                        // tokens emitted so far in this chunk
+    uint32_t blk;                         // current block index
+    uint32_t blk_tok0;                    // token index where the current block began
+    uint32_t blk_in0;                     // chunk-relative input offset where it began
+    uint32_t extra_lit;                   // 1 if the final position needs its own literal
+};
+
+__device__ __forceinline__ uint32_t ring_ld32(const uint32_t* ring32, uint32_t pos)
+{
+    uint32_t a = pos & 0xFFFFu, i = a >> 2;
+    uint32_t w0 = ring32[i], w1 = ring32[(i + 1) & (RING / 4 - 1)];
+    return __funnelshift_r(w0, w1, (a & 3u) * 8u);
+}
+__device__ __forceinline__ uint32_t ring_ld8(const uint32_t* ring32, uint32_t pos)
+{
+    return reinterpret_cast<const uint8_t*>(ring32)[pos & 0xFFFFu];
+}
+
+// length of the common prefix of the strings at stream positions p and c, at most maxlen
+__device__ __forceinline__ int match_len(const uint32_t* ring32, uint32_t p, uint32_t c, int maxlen)
+{
+    uint32_t ap = p & 0xFFFFu, ac = c & 0xFFFFu;
+    uint32_t ip = ap >> 2, ic = ac >> 2, sp = (ap & 3u) * 8u, sc = (ac & 3u) * 8u;
+    uint32_t p0 = ring32[ip], c0 = ring32[ic];
+    int l = 0;
+    while (l + 4 <= maxlen) {
+        ip = (ip + 1) & (RING / 4 - 1); ic = (ic + 1) & (RING / 4 - 1);
+        uint32_t p1 = ring32[ip], c1 = ring32[ic];
+        uint32_t x = __funnelshift_r(p0, p1, sp) ^ __funnelshift_r(c0, c1, sc);
+        if (x) return l + ((__ffs(x) - 1) >> 3);
+        l += 4; p0 = p1; c0 = c1;
+    }
+    while (l < maxlen && ring_ld8(ring32, p + l) == ring_ld8(ring32, c + l)) l++;
+    return l;
+}
+
+// Copy stream bytes [t*TILE, (t+1)*TILE) into the ring, zero beyond the end of the stream.
+// nthr threads of the caller cooperate (tid in [0, nthr)), 16 bytes per thread per step.
+__device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n_s, uint32_t t, uint32_t tid, uint32_t nthr)
+{
+    uint32_t base = t * TILE;
+    for (uint32_t o = tid * 16u; o < TILE; o += nthr * 16u) {
+        uint32_t pos = base + o;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (pos + 16u <= n_s) v = __ldg(reinterpret_cast<const uint4*>(sp + pos));
+        else if (pos < n_s) {
+            uint32_t w[4] = {0, 0, 0, 0};
+            for (uint32_t k = 0; pos + k < n_s; k++) w[k >> 2] |= (uint32_t)sp[pos + k] << ((k & 3u) * 8u);
+            v = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        *reinterpret_cast<uint4*>(&S.ring32[(pos & 0xFFFFu) >> 2]) = v;
+    }
+}
+
+// Insert the positions of tile t into the chain table and the 3-byte table, in stream order.
+// One warp; 32 consecutive positions per step; duplicates inside a step are linked by lane order.
+__device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane)
+{
+    uint32_t base = t * TILE;
+    uint32_t slot = base % LINK_RING + lane;
+    uint16_t* c3 = S.c3[t & 1];
+    for (uint32_t i = 0; i < GROUPS_PER_TILE; i++, slot += 32) {
+        uint32_t p = base + i * 32u + lane;
+        if (base + i * 32u >= n_s) break;                       // nothing past the end is ever searched
+        if (slot >= LINK_RING) slot -= LINK_RING;
+        uint32_t v = ring_ld32(S.ring32, p);
+        uint32_t h = hash4(v), h3 = hash3(v);
+        // 4-byte chains
+        uint32_t peers = __match_any_sync(FULL, h);
+        uint32_t lower = peers & ((1u << lane) - 1u);
+        uint32_t delta = 0;
+        if (lower) delta = lane - (31u - __clz(lower));
+        else {
+            uint32_t d = (p - (uint32_t)S.head[h]) & 0xFFFFu;
+            if (d != 0u && d <= 32767u && d <= p && hash4(ring_ld32(S.ring32, p - d)) == h) delta = d;
+        }
+        S.link[slot] = (uint16_t)delta;
+        if ((peers >> lane) == 1u) S.head[h] = (uint16_t)p;
+        // 3-byte single-entry table
+        uint32_t peers3 = __match_any_sync(FULL, h3);
+        uint32_t lower3 = peers3 & ((1u << lane) - 1u);
+        uint32_t d3 = 0;
+        if (lower3) d3 = lane - (31u - __clz(lower3));
+        else {
+            uint32_t d = (p - (uint32_t)S.head3[h3]) & 0xFFFFu;
+            if (d != 0u && d <= (uint32_t)TOO_FAR && d <= p && hash3(ring_ld32(S.ring32, p - d)) == h3) d3 = d;
+        }
+        c3[i * 32u + lane] = (uint16_t)d3;
+        if ((peers3 >> lane) == 1u) S.head3[h3] = (uint16_t)p;
+        __syncwarp();
+    }
+}
+
+// Best match for the 32 positions of one group (one warp).  Semantics: engine_model.c gzm_find_matches.
+__device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_t g, uint32_t n_s, uint32_t lane)
+{
+    uint32_t p = t * TILE + g * 32u + lane;
+    int maxlen = (p < n_s) ? min(258, (int)(n_s - p)) : 0;
+    int best = 2; uint32_t bdist = 0;
+    if (maxlen >= 3) {
+        uint32_t limit = min((uint32_t)MAXD, p);
+        int nice = min(lp.nice, maxlen);
+        int32_t slot = (int32_t)(p % LINK_RING);
+        uint32_t delta = S.link[slot];
+        uint32_t d = 0;
+        int depth = lp.depth;
+        uint32_t scan_end = ring_ld8(S.ring32, p + best);
+        while (delta != 0u && depth > 0) {
+            d += delta;
+            if (d > limit) break;
+            depth--;
+            uint32_t c = p - d;
+            slot -= (int32_t)delta; if (slot < 0) slot += LINK_RING;
+            if (best < maxlen && ring_ld8(S.ring32, c + best) == scan_end) {
+                int l = match_len(S.ring32, p, c, maxlen);
+                if (l > best) {
+                    best = l; bdist = d;
+                    if (l >= nice) break;
+                    scan_end = ring_ld8(S.ring32, p + best);
+                }
+            }
+            delta = S.link[slot];
+        }
+        if (best < 3 && lp.use_h3) {
+            uint32_t d3 = S.c3[t & 1][g * 32u + lane];
+            if (d3 != 0u && d3 <= min(limit, (uint32_t)TOO_FAR)) {
+                int l = match_len(S.ring32, p, p - d3, maxlen);
+                if (l >= 3) { best = l; bdist = d3; }
+            }
+        }
+        if (best == 3 && bdist > (uint32_t)TOO_FAR) best = 2;
+    }
+    uint32_t mi = p & (MRING - 1);
+    if (best >= 3) { S.mlen[mi] = (uint8_t)(best - 3); S.mdist[mi] = (uint16_t)(bdist - 1u); }
+    else { S.mlen[mi] = 0; S.mdist[mi] = 0xFFFFu; }
+}
+
+// next(p): the parse rule (engine_model.c gzm_parse).  Returns the step from p and whether p is a literal.
+__device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams& lp, uint32_t p, uint32_t n_s, bool& lit)
+{
+    uint32_t mi = p & (MRING - 1);
+    uint32_t md = S.mdist[mi];
+    uint32_t L = (uint32_t)S.mlen[mi] + 3u;
+    lit = (md == 0xFFFFu);
+    if (!lit && lp.lazy_parse && L < (uint32_t)lp.max_lazy && p + 1u < n_s) {
+        uint32_t mj = (p + 1u) & (MRING - 1);
+        if (S.mdist[mj] != 0xFFFFu && (uint32_t)S.mlen[mj] + 3u > L) lit = true;
+    }
+    return lit ? 1u : L;
+}
+
+// Walk from `start` inside [seg_lo, seg_hi); stop on leaving the segment or on reaching a position the
+// speculative walk of this segment already visited (then the rest of the path is the speculative one).
+__device__ __forceinline__ void seg_walk(const Smem& S, const LevelParams& lp, uint32_t n_s, int seg_lo, int seg_hi,
+                                         int start, unsigned long long spec_mask, int spec_exit,
+                                         unsigned long long& mask, int& exit_pos)
+{
+    unsigned long long m = 0ull;
+    int p = start;
+    while (p < seg_hi) {
+        unsigned long long bit = 1ull << (p - seg_lo);
+        if (spec_mask & bit) { mask = m | (spec_mask & ~(bit - 1ull)); exit_pos = spec_exit; return; }
+        m |= bit;
+        bool lit;
+        p += (int)parse_step(S, lp, (uint32_t)p, n_s, lit);
+    }
+    mask = m; exit_pos = p;
+}
+
+__device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid)
+{
+    // histograms of the block that just ended -> global; reset for the next one
+    for (uint32_t i = tid; i < 288u; i += LZ_THREADS) { brec->lfreq[i] = S.lfreq[i]; S.lfreq[i] = 0; }
+    if (tid < 32u) { brec->dfreq[tid] = S.dfreq[tid]; S.dfreq[tid] = 0; }
+    if (tid == 0) {
+        brec->tok_begin = S.blk_tok0; brec->tok_count = S.ntok - S.blk_tok0;
+        brec->in_off = S.blk_in0; brec->in_bytes = in_end - S.blk_in0;
+    }
+}
+
+__global__ void __launch_bounds__(LZ_THREADS, 1)
+k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
+       uint32_t* __restrict__ tokens, BlockRec* __restrict__ blocks, ChunkRec* __restrict__ chunks, LevelParams lp,
+       uint32_t* __restrict__ work_ctr)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem& S = *reinterpret_cast<Smem*>(smem_raw);
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) S.chunk_idx = atomicAdd(work_ctr, 1u);
+        __syncthreads();
+        const uint32_t c = S.chunk_idx;
+        if (c >= nchunks) break;
+
+        const uint64_t lo = (uint64_t)c * chunk;
+        const uint32_t nc = (uint32_t)min((uint64_t)chunk, n_bytes - lo);
+        const uint32_t D = dict ? (uint32_t)min((uint64_t)dict, lo + halo) : 0u;
+        const uint8_t* sp = in + lo - D;                 // stream = dictionary || chunk
+        const uint32_t n_s = D + nc;
+        const uint32_t ntiles = (n_s + TILE - 1) / TILE;
+        const uint32_t first_ctile = D / TILE;           // D is a multiple of TILE (0 or 32768)
+        const uint32_t nblocks = nc ? (nc + BLOCK_SPAN - 1) / BLOCK_SPAN : 1u;
+        uint32_t* tok = tokens + (size_t)c * chunk;
+        BlockRec* brecs = blocks + (size_t)c * bpc;
+
+        // ---- per-chunk reset ----
+        for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = 0;
+        for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = 0;
+        for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
+        if (tid < 32u) S.dfreq[tid] = 0;
+        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[0] = 0; S.grp_ctr[1] = 0; }
+        for (uint32_t t = 0; t < 3; t++) load_tile(S, sp, n_s, t, tid, LZ_THREADS);
+        __syncthreads();
+
+        // ---- pipeline: iteration k inserts tile k+1 while tile k is searched, then parses tile k ----
+        for (int k = -1; k < (int)ntiles; k++) {
+            // stage A
+            uint32_t* gctr = &S.grp_ctr[k & 1];
+            if (tid == 0) S.grp_ctr[(k + 1) & 1] = 0;           // last used two barriers ago
+            if (warp == 0) {
+                if (k + 1 < (int)ntiles) insert_tile(S, (uint32_t)(k + 1), n_s, lane);
+                load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
+            }
+            const bool ctile = k >= (int)first_ctile;
+            if (ctile) {
+                for (;;) {
+                    uint32_t g = 0;
+                    if (lane == 0) g = atomicAdd(gctr, 1u);
+                    g = __shfl_sync(FULL, g, 0);
+                    if (g >= (uint32_t)GROUPS_PER_TILE) break;
+                    if ((uint32_t)k * TILE + g * 32u >= n_s) continue;
+                    search_group(S, lp, (uint32_t)k, g, n_s, lane);
+                }
+            }
+            __syncthreads();
+            if (!ctile) continue;                       // uniform: dictionary tiles are insert-only
+
+            // stage B: parse tile k.  Decidable positions: [k*TILE-1, hi) (lazy needs mlen[p+1]).
+            const bool last = (k == (int)ntiles - 1);
+            const int base = k * TILE - 1;                        // -1 for the very first tile of a stream
+            const int hi = last ? (int)n_s : base + TILE;
+            const int hi_w = min(hi, base + TILE);                // what the 32 x 64 segments cover
+            // block boundary: tokens emitted from this tile on belong to the next block
+            const uint32_t q0 = (uint32_t)k * TILE - D;           // chunk-relative start of the tile
+            if (q0 != 0u && (q0 % BLOCK_SPAN) == 0u && S.blk + 1u < nblocks) {
+                flush_block(S, &brecs[S.blk], S.entry - D, tid);
+                __syncthreads();
+                if (tid == 0) { S.blk++; S.blk_tok0 = S.ntok; S.blk_in0 = S.entry - D; }
+                __syncthreads();
+            }
+            if (warp == 0) {
+                const int entry = (int)S.entry;                   // >= base by construction
+                const int seg_lo = base + 64 * (int)lane;
+                const int seg_hi = min(seg_lo + 64, hi_w);
+                // speculative walk: lane 0 starts at the true entry, the others at their segment start
+                const int spec_start = (lane == 0) ? entry : seg_lo;
+                unsigned long long spec_mask = 0ull, m = 0ull; int spec_exit = spec_start;
+                if (spec_start < seg_hi) seg_walk(S, lp, n_s, seg_lo, seg_hi, spec_start, 0ull, 0, spec_mask, spec_exit);
+                int x = spec_exit, assumed = -2;
+                for (;;) {
+                    int up = __shfl_up_sync(FULL, x, 1);
+                    int a = (lane == 0) ? entry : up;             // a >= seg_lo: exits never fall short of the next segment
+                    bool redo = (a != assumed);
+                    if (!__any_sync(FULL, redo)) break;
+                    if (redo) {
+                        assumed = a;
+                        if (a >= seg_hi) { m = 0ull; x = a; }
+                        else if (a == spec_start) { m = spec_mask; x = spec_exit; }
+                        else seg_walk(S, lp, n_s, seg_lo, seg_hi, a, spec_mask, spec_exit, m, x);
+                    }
+                }
+                uint32_t cnt = (uint32_t)__popcll(m), incl = cnt;
+                for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= (uint32_t)o) incl += v; }
+                S.masks[lane] = m;
+                S.seg_prefix[lane] = incl - cnt;
+                if (lane == 31) {
+                    S.seg_prefix[32] = incl;
+                    int e = x; uint32_t extra = 0;
+                    if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
+                    S.entry = (uint32_t)e; S.extra_lit = extra;
+                }
+            }
+            __syncthreads();
+            // emission: 2 positions per thread
+            {
+                const uint32_t ntok0 = S.ntok;
+#pragma unroll
+                for (int r = 0; r < 2; r++) {
+                    uint32_t o = tid * 2u + (uint32_t)r;
+                    uint32_t seg = o >> 6, bit = o & 63u;
+                    unsigned long long mk = S.masks[seg];
+                    if ((mk >> bit) & 1ull) {
+                        uint32_t idx = ntok0 + S.seg_prefix[seg] + (uint32_t)__popcll(mk & ((1ull << bit) - 1ull));
+                        uint32_t p = (uint32_t)(base + (int)o);
+                        bool lit; uint32_t step = parse_step(S, lp, p, n_s, lit);
+                        uint32_t tv;
+                        if (lit) { tv = ring_ld8(S.ring32, p); atomicAdd(&S.lfreq[tv], 1u); }
+                        else {
+                            uint32_t dist = (uint32_t)S.mdist[p & (MRING - 1)] + 1u;
+                            tv = tok_match(step, dist);
+                            atomicAdd(&S.lfreq[257u + len_code(step)], 1u);
+                            atomicAdd(&S.dfreq[dist_code(dist)], 1u);
+                        }
+                        tok[idx] = tv;
+                    }
+                }
+                if (tid == 0 && S.extra_lit) {
+                    uint32_t p = (uint32_t)(base + TILE);
+                    uint32_t tv = ring_ld8(S.ring32, p);
+                    atomicAdd(&S.lfreq[tv], 1u);
+                    tok[ntok0 + S.seg_prefix[32]] = tv;
+                }
+            }
+            __syncthreads();
+            if (tid == 0) { S.ntok += S.seg_prefix[32] + S.extra_lit; S.extra_lit = 0; }
+            __syncthreads();
+        }
+
+        // ---- chunk epilogue ----
+        flush_block(S, &brecs[S.blk], nc, tid);
+        if (tid == 0) {
+            ChunkRec* cr = &chunks[c];
+            cr->n_bytes = nc; cr->n_blocks = nblocks; cr->n_tokens = S.ntok;
+        }
+    }
+}
+
+}  // namespace
+
+cudaError_t lz77_configure()
+{
+    return cudaFuncSetAttribute(k_lz77, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+}
+
+void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
+                 uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st)
+{
+    uint32_t grid = nchunks < (uint32_t)n_sm ? nchunks : (uint32_t)n_sm;
+    if (grid == 0) return;
+    k_lz77<<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, tokens, blocks, chunks, lp, work_ctr);
+}
+
+}  // namespace gzb
