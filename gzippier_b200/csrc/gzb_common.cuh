@@ -141,13 +141,22 @@ __host__ __device__ __forceinline__ uint32_t gf2_mul(uint32_t a, uint32_t b)
     return p;
 }
 
+// multiply crc by x^(8*len) mod P; x2n[k] = x^(2^k) mod P
+__host__ __device__ __forceinline__ uint32_t crc_shift(const uint32_t* x2n, uint32_t crc, uint64_t len)
+{
+    uint64_t bits = len << 3;
+    for (int k = 0; bits; k++, bits >>= 1)
+        if (bits & 1u) crc = gf2_mul(x2n[k], crc);
+    return crc;
+}
+constexpr int CRC_TAB_WORDS = 1024 + 64;      // slice-by-4 tables followed by x^(2^k), k < 64
+
 // launchers (defined in the k_*.cu files)
-struct CrcTables;
-void launch_crc32(const uint8_t* in, uint64_t n_bytes, uint32_t chunk, uint32_t nchunks, ChunkRec* chunks, cudaStream_t st);
+void launch_crc32(const uint8_t* in, uint64_t n_bytes, uint32_t chunk, uint32_t nchunks, ChunkRec* chunks, const uint32_t* d_tab, cudaStream_t st);
 void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st);
 void launch_huffman(BlockRec* blocks, const ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, cudaStream_t st);
-void launch_layout(BlockRec* blocks, ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, uint32_t chunk, int final, Cursor* cur, cudaStream_t st);
+void launch_layout(BlockRec* blocks, ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, int final, Cursor* cur, const uint32_t* d_tab, cudaStream_t st);
 void launch_pack(const uint8_t* in, uint32_t chunk, const uint32_t* tokens, const BlockRec* blocks, const ChunkRec* chunks,
                  uint32_t nchunks, uint32_t bpc, uint8_t* out, cudaStream_t st);
 cudaError_t lz77_configure();

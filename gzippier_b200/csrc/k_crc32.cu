@@ -13,30 +13,24 @@
 
 namespace gzb {
 
-__constant__ uint32_t c_crc_table[4][256];   // slice-by-4 tables (make_crc_table, lib/zlib/crc32.c:89-135)
-__constant__ uint32_t c_x2n[64];             // x^(2^k) mod P
+// Tables live in global memory (built once per context by the host, gzb_api.cu):
+//   tab[0..1023]    slice-by-4 tables (same construction as make_crc_table, lib/zlib/crc32.c:89-135)
+//   tab[1024..1087] x^(2^k) mod P, k = 0..63
 
 namespace {
 
 constexpr int CRC_THREADS = 256;
 
-// multiply crc by x^(8*len) mod P
-__device__ __forceinline__ uint32_t crc_shift(uint32_t crc, uint64_t len)
-{
-    uint64_t bits = len << 3;
-    for (int k = 0; bits; k++, bits >>= 1)
-        if (bits & 1u) crc = gf2_mul(c_x2n[k], crc);
-    return crc;
-}
-
 __global__ void __launch_bounds__(CRC_THREADS)
-k_crc32(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t chunk, ChunkRec* __restrict__ chunks)
+k_crc32(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t chunk, ChunkRec* __restrict__ chunks, const uint32_t* __restrict__ g_tab)
 {
     __shared__ uint32_t tab[4][256];
+    __shared__ uint32_t x2n[64];
     __shared__ uint32_t s_crc[CRC_THREADS];
     __shared__ uint32_t s_len[CRC_THREADS];
     const uint32_t tid = threadIdx.x;
-    for (uint32_t i = tid; i < 1024u; i += CRC_THREADS) (&tab[0][0])[i] = (&c_crc_table[0][0])[i];
+    for (uint32_t i = tid; i < 1024u; i += CRC_THREADS) (&tab[0][0])[i] = g_tab[i];
+    if (tid < 64u) x2n[tid] = g_tab[1024u + tid];
     __syncthreads();
 
     const uint64_t lo = (uint64_t)blockIdx.x * chunk;
@@ -62,7 +56,7 @@ k_crc32(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t chunk, ChunkR
     for (uint32_t stride = 1; stride < CRC_THREADS; stride <<= 1) {
         if ((tid & (2u * stride - 1u)) == 0u) {
             uint32_t lenB = s_len[tid + stride];
-            s_crc[tid] = crc_shift(s_crc[tid], lenB) ^ s_crc[tid + stride];
+            s_crc[tid] = crc_shift(x2n, s_crc[tid], lenB) ^ s_crc[tid + stride];
             s_len[tid] += lenB;
         }
         __syncthreads();
@@ -72,10 +66,10 @@ k_crc32(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t chunk, ChunkR
 
 }  // namespace
 
-void launch_crc32(const uint8_t* in, uint64_t n_bytes, uint32_t chunk, uint32_t nchunks, ChunkRec* chunks, cudaStream_t st)
+void launch_crc32(const uint8_t* in, uint64_t n_bytes, uint32_t chunk, uint32_t nchunks, ChunkRec* chunks, const uint32_t* d_tab, cudaStream_t st)
 {
     if (nchunks == 0) return;
-    k_crc32<<<nchunks, CRC_THREADS, 0, st>>>(in, n_bytes, chunk, chunks);
+    k_crc32<<<nchunks, CRC_THREADS, 0, st>>>(in, n_bytes, chunk, chunks, d_tab);
 }
 
 }  // namespace gzb

@@ -1,0 +1,264 @@
+// k_huffman.cu -- per deflate block: length-limited Huffman codes, code-length header, block-type choice.
+//
+// Replaces build_tree / gen_bitlen / gen_codes (lib/zlib/trees.c:615-697, 486-562, 572-605),
+// scan_tree / send_tree / build_bl_tree / send_all_trees (:703-858) and the stored/static/dynamic
+// decision of _tr_flush_block (:911-1008).  Not a port: zlib builds the tree with a heap and repairs
+// over-long codes by moving leaves; here the symbols are sorted by a warp-wide bitonic network,
+// code lengths come from the in-place Moffat-Katajainen pass over the sorted frequencies, and the
+// 15-bit (7-bit for the code-length alphabet) limit is enforced on the count-per-length vector with
+// a Kraft-sum repair.  oracle/engine_model.c (gzm_plan_block) is the sequential statement.
+//
+// One warp per block.  The serial parts run on lane 0; they are a few thousand dependent steps per
+// block and there are tens of thousands of blocks in flight, so the stage is latency-tolerant
+// (measured share of the pipeline: profiles/).
+#include "gzb_common.cuh"
+
+namespace gzb {
+
+namespace {
+
+constexpr uint32_t FULL = 0xFFFFFFFFu;
+__constant__ uint8_t c_bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+
+struct HuffSmem {
+    uint32_t key[512];        // sort keys: freq << 9 | symbol
+    uint32_t A[288];          // sorted frequencies -> code lengths (in place)
+    uint32_t ftmp[288];       // working copy of a histogram (forced symbols live only here)
+    uint32_t lfreq[288];
+    uint32_t dfreq[32];
+    uint32_t bfreq[19];
+    uint8_t  llen[288], dlen[32], blen[19];
+    uint16_t bcode[19];
+    uint8_t  rsym[320], rext[320];
+    uint8_t  header[HDR_BYTES];
+};
+
+// ---- bitonic sort of 512 keys by one warp ----
+__device__ void warp_sort512(uint32_t* key, uint32_t lane)
+{
+    for (uint32_t k = 2; k <= 512u; k <<= 1) {
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = lane; t < 256u; t += 32u) {
+                uint32_t i = ((t & ~(j - 1u)) << 1) | (t & (j - 1u));    // index with bit j clear
+                uint32_t l = i | j;
+                uint32_t a = key[i], b = key[l];
+                bool up = ((i & k) == 0u);
+                if ((a > b) == up) { key[i] = b; key[l] = a; }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// In-place minimum-redundancy code lengths (Moffat & Katajainen); A sorted ascending.
+__device__ void min_redundancy(uint32_t* A, int n)
+{
+    int root, leaf, next, avbl, used, dpth;
+    if (n == 0) return;
+    if (n == 1) { A[0] = 1; return; }
+    A[0] += A[1]; root = 0; leaf = 2;
+    for (next = 1; next < n - 1; next++) {
+        if (leaf >= n || A[root] < A[leaf]) { A[next] = A[root]; A[root++] = (uint32_t)next; } else A[next] = A[leaf++];
+        if (leaf >= n || (root < next && A[root] < A[leaf])) { A[next] += A[root]; A[root++] = (uint32_t)next; } else A[next] += A[leaf++];
+    }
+    A[n - 2] = 0;
+    for (next = n - 3; next >= 0; next--) A[next] = A[A[next]] + 1;
+    avbl = 1; used = dpth = 0; root = n - 2; next = n - 1;
+    while (avbl > 0) {
+        while (root >= 0 && (int)A[root] == dpth) { used++; root--; }
+        while (avbl > used) { A[next--] = (uint32_t)dpth; avbl--; }
+        avbl = 2 * used; dpth++; used = 0;
+    }
+}
+
+// freq[0..nsym) -> lens[0..nsym) limited to maxbits; forces >= 2 coded symbols (trees.c:646-651).
+// Whole warp calls; returns the highest coded symbol.
+__device__ int huff_lengths(HuffSmem& S, const uint32_t* freq_in, int nsym, int maxbits, uint8_t* lens, uint32_t lane)
+{
+    uint32_t* freq = S.ftmp;
+    for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) freq[i] = freq_in[i];
+    __syncwarp();
+    if (lane == 0) {
+        int used = 0;
+        for (int i = 0; i < nsym; i++) used += freq[i] != 0u;
+        for (int i = 0; used < 2 && i < nsym; i++) if (!freq[i]) { freq[i] = 1; used++; }
+    }
+    __syncwarp();
+    for (uint32_t i = lane; i < 512u; i += 32u)
+        S.key[i] = (i < (uint32_t)nsym && freq[i]) ? ((freq[i] << 9) | i) : 0xFFFFFFFFu;
+    for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) lens[i] = 0;
+    __syncwarp();
+    warp_sort512(S.key, lane);
+    int n = 0;
+    for (uint32_t i = lane; i < 512u; i += 32u) n += S.key[i] != 0xFFFFFFFFu;
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(FULL, n, o);
+    for (uint32_t i = lane; i < (uint32_t)n; i += 32u) S.A[i] = S.key[i] >> 9;
+    __syncwarp();
+    int maxsym = 0;
+    if (lane == 0) {
+        min_redundancy(S.A, n);
+        int num[33];
+        for (int i = 0; i <= 32; i++) num[i] = 0;
+        for (int i = 0; i < n; i++) { uint32_t l = S.A[i]; num[l > 32u ? 32 : l]++; }
+        if (n > 1) {
+            for (int i = maxbits + 1; i <= 32; i++) { num[maxbits] += num[i]; num[i] = 0; }
+            uint32_t total = 0;
+            for (int i = maxbits; i > 0; i--) total += (uint32_t)num[i] << (maxbits - i);
+            while (total != (1u << maxbits)) {
+                num[maxbits]--;
+                for (int i = maxbits - 1; i > 0; i--) if (num[i]) { num[i]--; num[i + 1] += 2; break; }
+                total--;
+            }
+        }
+        int j = n;
+        for (int i = 1; i <= maxbits; i++) for (int l = num[i]; l > 0; l--) lens[S.key[--j] & 511u] = (uint8_t)i;
+        for (int i = 0; i < nsym; i++) if (lens[i]) maxsym = i;
+    }
+    maxsym = __shfl_sync(FULL, maxsym, 0);
+    __syncwarp();
+    return maxsym;
+}
+
+// canonical codes, bit-reversed for LSB-first emission; lane 0 only
+__device__ void huff_codes(const uint8_t* lens, int nsym, int maxbits, uint16_t* codes)
+{
+    int cnt[16], next[16];
+    for (int i = 0; i < 16; i++) cnt[i] = 0;
+    for (int i = 0; i < nsym; i++) cnt[lens[i]]++;
+    cnt[0] = 0;
+    int code = 0;
+    for (int b = 1; b <= maxbits; b++) { code = (code + cnt[b - 1]) << 1; next[b] = code; }
+    for (int i = 0; i < nsym; i++) {
+        int l = lens[i];
+        if (!l) { codes[i] = 0; continue; }
+        uint32_t c = (uint32_t)next[l]++;
+        codes[i] = (uint16_t)(__brev(c) >> (32 - l));
+    }
+}
+
+// RLE of code lengths (scan_tree/send_tree, trees.c:703-793); lane 0 only
+__device__ int rle_lengths(const uint8_t* lens, int n, uint8_t* sym, uint8_t* ext)
+{
+    int k = 0, prevlen = -1, curlen, nextlen = lens[0], count = 0, max_count = 7, min_count = 4;
+    if (nextlen == 0) { max_count = 138; min_count = 3; }
+    for (int i = 0; i < n; i++) {
+        curlen = nextlen; nextlen = (i + 1 < n) ? lens[i + 1] : 0xffff;
+        if (++count < max_count && curlen == nextlen) continue;
+        else if (count < min_count) { while (count--) { sym[k] = (uint8_t)curlen; ext[k++] = 0; } }
+        else if (curlen != 0) {
+            if (curlen != prevlen) { sym[k] = (uint8_t)curlen; ext[k++] = 0; count--; }
+            sym[k] = 16; ext[k++] = (uint8_t)(count - 3);
+        } else if (count <= 10) { sym[k] = 17; ext[k++] = (uint8_t)(count - 3); }
+        else { sym[k] = 18; ext[k++] = (uint8_t)(count - 11); }
+        count = 0; prevlen = curlen;
+        if (nextlen == 0) { max_count = 138; min_count = 3; }
+        else if (curlen == nextlen) { max_count = 6; min_count = 3; }
+        else { max_count = 7; min_count = 4; }
+    }
+    return k;
+}
+
+struct BitW { uint8_t* out; uint32_t bitpos; };
+__device__ __forceinline__ void putbits(BitW& w, uint32_t v, int n)
+{
+    for (int i = 0; i < n; i++, w.bitpos++) {
+        if ((w.bitpos & 7u) == 0u) w.out[w.bitpos >> 3] = 0;
+        w.out[w.bitpos >> 3] |= (uint8_t)(((v >> i) & 1u) << (w.bitpos & 7u));
+    }
+}
+
+__device__ __forceinline__ uint32_t static_llen(uint32_t i) { return i < 144u ? 8u : i < 256u ? 9u : i < 280u ? 7u : 8u; }
+
+__global__ void __launch_bounds__(32)
+k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, uint32_t bpc)
+{
+    __shared__ HuffSmem S;
+    const uint32_t lane = threadIdx.x;
+    const uint32_t c = blockIdx.x / bpc, b = blockIdx.x % bpc;
+    if (b >= chunks[c].n_blocks) return;
+    BlockRec* B = &blocks[blockIdx.x];
+
+    for (uint32_t i = lane; i < 288u; i += 32u) S.lfreq[i] = (i < (uint32_t)NLSYM) ? B->lfreq[i] : 0u;
+    S.dfreq[lane] = (lane < (uint32_t)NDSYM) ? B->dfreq[lane] : 0u;
+    __syncwarp();
+    if (lane == 0) S.lfreq[256] = 1;                       // EOB (init_block, trees.c:407-420)
+    __syncwarp();
+
+    int maxl = huff_lengths(S, S.lfreq, NLSYM, 15, S.llen, lane);
+    int maxd = huff_lengths(S, S.dfreq, NDSYM, 15, S.dlen, lane);
+    if (maxl < 256) maxl = 256;
+    const int hlit = maxl + 1, hdist = maxd + 1;
+
+    // code-length alphabet
+    int nrle = 0;
+    if (lane == 0) {
+        int k1 = rle_lengths(S.llen, hlit, S.rsym, S.rext);
+        int k2 = rle_lengths(S.dlen, hdist, S.rsym + k1, S.rext + k1);
+        nrle = k1 + k2;
+        for (int i = 0; i < 19; i++) S.bfreq[i] = 0;
+        for (int i = 0; i < nrle; i++) S.bfreq[S.rsym[i]]++;
+    }
+    nrle = __shfl_sync(FULL, nrle, 0);
+    __syncwarp();
+    huff_lengths(S, S.bfreq, 19, 7, S.blen, lane);
+
+    if (lane == 0) {
+        int hclen = 19;
+        while (hclen > 4 && S.blen[c_bl_order[hclen - 1]] == 0) hclen--;
+        huff_codes(S.blen, 19, 7, S.bcode);
+        BitW w = {S.header, 0};
+        putbits(w, (uint32_t)(hlit - 257), 5); putbits(w, (uint32_t)(hdist - 1), 5); putbits(w, (uint32_t)(hclen - 4), 4);
+        for (int i = 0; i < hclen; i++) putbits(w, S.blen[c_bl_order[i]], 3);
+        for (int i = 0; i < nrle; i++) {
+            uint32_t sy = S.rsym[i];
+            putbits(w, S.bcode[sy], S.blen[sy]);
+            if (sy == 16u) putbits(w, S.rext[i], 2); else if (sy == 17u) putbits(w, S.rext[i], 3); else if (sy == 18u) putbits(w, S.rext[i], 7);
+        }
+        const uint32_t header_bits = w.bitpos;
+        // sizes in bits (header included, 3 type bits excluded)
+        unsigned long long dyn = header_bits, sta = 0;
+        for (uint32_t i = 0; i < (uint32_t)NLSYM; i++) {
+            uint32_t ex = i >= 257u ? len_extra_bits(i - 257u) : 0u;
+            dyn += (unsigned long long)S.lfreq[i] * (S.llen[i] + ex);
+            sta += (unsigned long long)S.lfreq[i] * (static_llen(i) + ex);
+        }
+        for (uint32_t i = 0; i < (uint32_t)NDSYM; i++) {
+            uint32_t ex = dist_extra_bits(i);
+            dyn += (unsigned long long)S.dfreq[i] * (S.dlen[i] + ex);
+            sta += (unsigned long long)S.dfreq[i] * (5u + ex);
+        }
+        // choice (cf. trees.c:945-993): bytes rounded up, 3 type bits included
+        const uint32_t in_bytes = B->in_bytes;
+        unsigned long long dyn_b = (dyn + 3 + 7) >> 3, sta_b = (sta + 3 + 7) >> 3;
+        unsigned long long nsub = in_bytes ? (in_bytes + 65534u) / 65535u : 1u;
+        unsigned long long sto_b = in_bytes + 5ull * nsub;
+        unsigned long long bestb = dyn_b < sta_b ? dyn_b : sta_b;
+        uint32_t type = (sto_b <= bestb) ? 0u : (sta_b <= dyn_b) ? 1u : 2u;
+        B->type = type;
+        B->header_bits = header_bits;
+        B->body_bits = (type == 2u) ? dyn : (type == 1u) ? sta : 0ull;
+        S.key[0] = type;
+    }
+    __syncwarp();
+    const uint32_t type = S.key[0];
+    __syncwarp();
+    if (type == 1u) {
+        for (uint32_t i = lane; i < 288u; i += 32u) S.llen[i] = (uint8_t)static_llen(i);
+        S.dlen[lane] = (lane < (uint32_t)NDSYM) ? 5 : 0;
+        __syncwarp();
+    }
+    if (lane == 0) { huff_codes(S.llen, type == 1u ? 288 : NLSYM, 15, B->lcode); huff_codes(S.dlen, NDSYM, 15, B->dcode); }
+    for (uint32_t i = lane; i < 288u; i += 32u) B->llen[i] = (i < (uint32_t)NLSYM || type == 1u) ? S.llen[i] : 0;
+    B->dlen[lane] = (lane < (uint32_t)NDSYM) ? S.dlen[lane] : 0;
+    for (uint32_t i = lane; i < (uint32_t)HDR_BYTES; i += 32u) B->header[i] = S.header[i];
+}
+
+}  // namespace
+
+void launch_huffman(BlockRec* blocks, const ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, cudaStream_t st)
+{
+    if (nchunks == 0) return;
+    k_huffman<<<nchunks * bpc, 32, 0, st>>>(blocks, chunks, bpc);
+}
+
+}  // namespace gzb

@@ -346,10 +346,14 @@ size_t gzm_deflate_chunk(const gzm_params *P, const uint8_t *stream, int D, int 
     bitw w = {out, 0};
     int nblocks = n ? (n + P->block_span - 1) / P->block_span : 1;
     int ti = 0, last_type = -1;
+    /* block b holds the tokens that start in [b*span-1, (b+1)*span-1) -- the positions the kernel decides
+     * while it parses the tiles of span b (the last byte of a tile waits for its successor's match);
+     * its input range runs from its first token to the first token of the next block. */
+    uint32_t lo = 0;
     for (int b = 0; b < nblocks; b++) {
-        uint32_t lo = (uint32_t)b * (uint32_t)P->block_span, hi = lo + (uint32_t)P->block_span;
-        if (hi > (uint32_t)n) hi = (uint32_t)n;
-        int t0 = ti; while (ti < nt && tpos[ti] < hi) ti++;
+        int t0 = ti;
+        while (ti < nt && (b == nblocks - 1 || (int)((tpos[ti] + 1) / (uint32_t)P->block_span) <= b)) ti++;
+        uint32_t hi = (ti < nt) ? tpos[ti] : (uint32_t)n;
         uint32_t lf[286] = {0}, df[30] = {0};
         for (int i = t0; i < ti; i++) {
             uint32_t t = tok[i];
@@ -361,6 +365,7 @@ size_t gzm_deflate_chunk(const gzm_params *P, const uint8_t *stream, int D, int 
         emit_block(&w, &B, chunk + lo, hi - lo, tok + t0, ti - t0, bfinal);
         last_type = B.type;
         if (st) { st->blocks[B.type]++; }
+        lo = hi;
     }
     if (final) { while (w.bitpos & 7) putbits(&w, 0, 1); }
     else if (w.bitpos & 7) {          /* byte-align with an empty stored block (cf. Z_SYNC_FLUSH, parallel.c:624-644) */

@@ -7,10 +7,10 @@
 extern "C" {
 #endif
 
-#define GZM_HBITS       15
+#define GZM_HBITS       14
 #define GZM_H3BITS      12                        /* single-entry table of most recent 3-byte twins */
 #define GZM_TILE        2048                      /* positions per pipeline step of the LZ77 kernel */
-#define GZM_MAXD        (32768 - GZM_TILE)        /* farthest match the kernel can follow           */
+#define GZM_MAXD        32768                     /* farthest match (the link ring is 32768+2*TILE) */
 #define GZM_TOO_FAR     4096                      /* lib/zlib/deflate.c:110-112                      */
 #define GZM_BLOCK_SPAN  65536                     /* input bytes per deflate block                   */
 
