@@ -1,0 +1,501 @@
+// gzb_api.cu -- the C ABI of include/gzb200.h: context, scratch memory, kernel orchestration.
+//
+// Stands where compress_thread's per-job body stands in the reference (src/parallel.c:595-688) and
+// where its buffer pools stand (:327-347).  Everything here is plumbing; the arithmetic is in k_*.cu.
+#include "gzb_common.cuh"
+#include "gzb200.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+using namespace gzb;
+
+namespace {
+
+constexpr int MAX_SUB = 64;                       // stage-timing slots (sub-batches timed per call)
+
+struct Scratch {
+    uint32_t*  tokens = nullptr;
+    BlockRec*  blocks = nullptr;
+    ChunkRec*  chunks = nullptr;
+    uint32_t   cap_chunks = 0, chunk = 0;
+};
+
+}  // namespace
+
+struct gzb_ctx {
+    int device = 0, n_sm = 0;
+    cudaStream_t stream = nullptr;
+    uint32_t* d_tab = nullptr;                    // CRC tables (CRC_TAB_WORDS words)
+    uint32_t  h_x2n[64];
+    Scratch   scr;
+    Cursor*   d_cursor = nullptr;
+    Cursor*   h_cursor = nullptr;                 // pinned
+    uint32_t* d_work = nullptr;                   // one work counter per sub-batch
+    uint32_t  batch_chunks = 4096;                // sub-batch size (GZB_BATCH_CHUNKS)
+    cudaEvent_t ev[MAX_SUB][6];
+    int       n_sub_timed = 0;
+    bool      pending = false;
+    uint64_t  pending_n = 0;
+    cudaStream_t pending_stream = nullptr;
+    // host path staging
+    uint8_t *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
+    uint64_t stage_in_cap = 0, stage_out_cap = 0;
+    char      err[512];
+    std::mutex mu;
+};
+
+namespace {
+
+int fail(gzb_ctx* ctx, int code, const char* what, cudaError_t ce = cudaSuccess)
+{
+    if (ctx) {
+        if (ce != cudaSuccess) snprintf(ctx->err, sizeof(ctx->err), "%s: %s", what, cudaGetErrorString(ce));
+        else snprintf(ctx->err, sizeof(ctx->err), "%s", what);
+    }
+    return code;
+}
+#define CU(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail((ctx), GZB_E_CUDA, #call, e_); } while (0)
+
+void build_crc_tables(uint32_t* tab /* CRC_TAB_WORDS */)
+{
+    for (uint32_t n = 0; n < 256; n++) {
+        uint32_t c = n;
+        for (int k = 0; k < 8; k++) c = (c & 1u) ? CRC_POLY ^ (c >> 1) : c >> 1;
+        tab[n] = c;
+    }
+    for (uint32_t n = 0; n < 256; n++) {
+        uint32_t c = tab[n];
+        for (int k = 1; k < 4; k++) { c = tab[c & 0xFFu] ^ (c >> 8); tab[k * 256 + n] = c; }
+    }
+    uint32_t p = 1u << 30;                        // x^1
+    tab[1024] = p;
+    for (int k = 1; k < 64; k++) { p = gf2_mul(p, p); tab[1024 + k] = p; }
+}
+
+const LevelParams& level_params(int level)
+{
+    // good/lazy/nice: the reference's configuration_table (lib/zlib/deflate.c:134-146).
+    // depth: candidates examined per position (every position is searched, chains keyed on 4 bytes).
+    static const LevelParams t[10] = {
+        {0, 0, 0, 0, 0},
+        {1, 8, 4, 0, 1},   {2, 16, 5, 0, 1},   {4, 32, 6, 0, 1},
+        {8, 16, 4, 1, 1},  {16, 32, 16, 1, 1}, {32, 128, 16, 1, 1},
+        {40, 128, 32, 1, 1}, {64, 258, 128, 1, 1}, {96, 258, 258, 1, 1}};
+    return t[level];
+}
+
+int ensure_scratch(gzb_ctx* ctx, uint32_t nchunks, uint32_t chunk)
+{
+    Scratch& s = ctx->scr;
+    if (s.cap_chunks >= nchunks && s.chunk == chunk) return GZB_OK;
+    cudaFree(s.tokens); cudaFree(s.blocks); cudaFree(s.chunks);
+    s = Scratch();
+    const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
+    cudaError_t e;
+    if ((e = cudaMalloc(&s.tokens, (size_t)nchunks * chunk * sizeof(uint32_t))) != cudaSuccess ||
+        (e = cudaMalloc(&s.blocks, (size_t)nchunks * bpc * sizeof(BlockRec))) != cudaSuccess ||
+        (e = cudaMalloc(&s.chunks, (size_t)nchunks * sizeof(ChunkRec))) != cudaSuccess) {
+        cudaFree(s.tokens); cudaFree(s.blocks); cudaFree(s.chunks); s = Scratch();
+        (void)cudaGetLastError();
+        return fail(ctx, GZB_E_NOMEM, "cudaMalloc(scratch)", e);
+    }
+    s.cap_chunks = nchunks; s.chunk = chunk;
+    return GZB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* gzb_strerror(int code)
+{
+    switch (code) {
+    case GZB_OK: return "ok";
+    case GZB_E_ARG: return "bad argument";
+    case GZB_E_LEVEL: return "compression level must be 1..9";
+    case GZB_E_NOMEM: return "out of memory";
+    case GZB_E_CUDA: return "CUDA error";
+    case GZB_E_NO_DEVICE: return "no usable CUDA device (there is no CPU fallback)";
+    case GZB_E_OUT_FULL: return "output buffer smaller than gzb_bound()";
+    case GZB_E_IO: return "I/O error";
+    default: return "unknown error";
+    }
+}
+
+const char* gzb_last_error(const gzb_ctx* ctx) { return ctx ? ctx->err : "no context"; }
+
+int gzb_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+    return n;
+}
+
+uint64_t gzb_bound(uint64_t n, uint32_t flags)
+{
+    // worst case per block: stored, 5 bytes per <=65535-byte sub-block, + 5 bytes of alignment block per chunk
+    const uint64_t chunk = (flags & GZB_F_RSYNCABLE) ? GZB_RSYNC_CHUNK : GZB_CHUNK;
+    const uint64_t nchunks = n ? (n + chunk - 1) / chunk : 1;
+    const uint64_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
+    return n + nchunks * (bpc * 2 * 5 + 5 + 4) + 64;
+}
+
+int gzb_create(int device, gzb_ctx** out)
+{
+    if (!out) return GZB_E_ARG;
+    *out = nullptr;
+    int ndev = gzb_device_count();
+    if (ndev <= 0 || device < 0 || device >= ndev) return GZB_E_NO_DEVICE;
+    gzb_ctx* ctx = new (std::nothrow) gzb_ctx();
+    if (!ctx) return GZB_E_NOMEM;
+    ctx->err[0] = 0; ctx->device = device;
+    memset(ctx->ev, 0, sizeof(ctx->ev));
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return GZB_E_NO_DEVICE; }
+    if (prop.major < 10) { delete ctx; return GZB_E_NO_DEVICE; }     // sm_100a code only
+    ctx->n_sm = prop.multiProcessorCount;
+    const char* bc = getenv("GZB_BATCH_CHUNKS");
+    if (bc && atoi(bc) > 0) ctx->batch_chunks = (uint32_t)atoi(bc);
+    uint32_t tab[CRC_TAB_WORDS];
+    build_crc_tables(tab);
+    memcpy(ctx->h_x2n, tab + 1024, sizeof(ctx->h_x2n));
+    bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaMalloc(&ctx->d_tab, sizeof(tab)) == cudaSuccess &&
+              cudaMemcpy(ctx->d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice) == cudaSuccess &&
+              cudaMalloc(&ctx->d_cursor, sizeof(Cursor)) == cudaSuccess &&
+              cudaMallocHost(&ctx->h_cursor, sizeof(Cursor)) == cudaSuccess &&
+              cudaMalloc(&ctx->d_work, sizeof(uint32_t) * 65536) == cudaSuccess &&
+              lz77_configure() == cudaSuccess;
+    for (int i = 0; ok && i < MAX_SUB; i++) for (int j = 0; j < 6; j++) ok = ok && cudaEventCreate(&ctx->ev[i][j]) == cudaSuccess;
+    if (!ok) { (void)cudaGetLastError(); gzb_destroy(ctx); return GZB_E_CUDA; }
+    *out = ctx;
+    return GZB_OK;
+}
+
+void gzb_destroy(gzb_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->scr.tokens); cudaFree(ctx->scr.blocks); cudaFree(ctx->scr.chunks);
+    cudaFree(ctx->d_tab); cudaFree(ctx->d_cursor); cudaFree(ctx->d_work);
+    cudaFree(ctx->d_in); cudaFree(ctx->d_out);
+    if (ctx->h_cursor) cudaFreeHost(ctx->h_cursor);
+    if (ctx->h_in) cudaFreeHost(ctx->h_in);
+    if (ctx->h_out) cudaFreeHost(ctx->h_out);
+    for (int i = 0; i < MAX_SUB; i++) for (int j = 0; j < 6; j++) if (ctx->ev[i][j]) cudaEventDestroy(ctx->ev[i][j]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    (void)cudaGetLastError();
+    delete ctx;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// device-resident path
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+// Enqueue the whole pipeline for d_in[0, n) on `st`.  No host synchronisation.
+int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
+                    uint8_t* d_out, uint64_t out_cap, cudaStream_t st)
+{
+    if (level < 1 || level > 9) return fail(ctx, GZB_E_LEVEL, "level must be 1..9");
+    const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
+    const uint32_t chunk = rs ? GZB_RSYNC_CHUNK : GZB_CHUNK, dict = rs ? 0u : GZB_DICT;
+    if (n && (!d_in || !d_out)) return fail(ctx, GZB_E_ARG, "null buffer");
+    if (((uintptr_t)d_in & 15u) || ((uintptr_t)d_out & 15u)) return fail(ctx, GZB_E_ARG, "d_in and d_out must be 16-byte aligned");
+    if (halo != 0u && halo != dict) return fail(ctx, GZB_E_ARG, "halo must be 0 or the dictionary size");
+    if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const uint64_t nchunks64 = (n + chunk - 1) / chunk;
+    const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
+    const LevelParams lp = level_params(level);
+    ctx->n_sub_timed = 0;
+
+    CU(ctx, cudaMemsetAsync(ctx->d_cursor, 0, sizeof(Cursor), st));
+    if (n == 0) {
+        // empty input: the member body is one final static block holding only EOB -- "03 00", what the
+        // reference's single-stream path writes (its -j path deadlocks here)
+        static const uint8_t empty_final[2] = {0x03, 0x00};
+        Cursor c; memset(&c, 0, sizeof(c));
+        if (flags & GZB_F_FINAL) {
+            if (!d_out) return fail(ctx, GZB_E_ARG, "null buffer");
+            CU(ctx, cudaMemcpyAsync(d_out, empty_final, 2, cudaMemcpyHostToDevice, st));
+            c.out_bytes = 2; c.n_blocks = 1;
+        }
+        CU(ctx, cudaStreamSynchronize(st));
+        *ctx->h_cursor = c;
+        return GZB_OK;
+    }
+    const uint32_t sub = (uint32_t)(nchunks64 < ctx->batch_chunks ? nchunks64 : ctx->batch_chunks);
+    int rc = ensure_scratch(ctx, sub, chunk);
+    if (rc != GZB_OK) return rc;
+    const uint64_t nsub = (nchunks64 + sub - 1) / sub;
+    if (nsub > 65536) return fail(ctx, GZB_E_ARG, "input too large for one call");
+    // k_pack ORs bits into the output: zero everything that can be written
+    CU(ctx, cudaMemsetAsync(d_out, 0, gzb_bound(n, flags), st));
+    CU(ctx, cudaMemsetAsync(ctx->d_work, 0, sizeof(uint32_t) * nsub, st));
+
+    for (uint64_t sb = 0; sb < nsub; sb++) {
+        const uint64_t c0 = sb * sub;
+        const uint32_t nch = (uint32_t)((nchunks64 - c0) < sub ? (nchunks64 - c0) : sub);
+        const uint64_t off = c0 * chunk;
+        const uint64_t nb = (n - off) < (uint64_t)nch * chunk ? (n - off) : (uint64_t)nch * chunk;
+        const uint32_t h = (sb == 0) ? halo : dict;
+        const int fin = ((flags & GZB_F_FINAL) && sb == nsub - 1) ? 1 : 0;
+        const bool timed = sb < (uint64_t)MAX_SUB;
+        cudaEvent_t* ev = ctx->ev[timed ? sb : 0];
+        if (timed) { CU(ctx, cudaEventRecord(ev[0], st)); }
+        launch_crc32(d_in + off, nb, chunk, nch, ctx->scr.chunks, ctx->d_tab, st);
+        if (timed) { CU(ctx, cudaEventRecord(ev[1], st)); }
+        launch_lz77(d_in + off, nb, h, chunk, dict, nch, ctx->scr.tokens, ctx->scr.blocks, ctx->scr.chunks, lp,
+                    ctx->d_work + sb, ctx->n_sm, st);
+        if (timed) { CU(ctx, cudaEventRecord(ev[2], st)); }
+        launch_huffman(ctx->scr.blocks, ctx->scr.chunks, nch, bpc, st);
+        if (timed) { CU(ctx, cudaEventRecord(ev[3], st)); }
+        launch_layout(ctx->scr.blocks, ctx->scr.chunks, nch, bpc, fin, ctx->d_cursor, ctx->d_tab, st);
+        if (timed) { CU(ctx, cudaEventRecord(ev[4], st)); }
+        launch_pack(d_in + off, chunk, ctx->scr.tokens, ctx->scr.blocks, ctx->scr.chunks, nch, bpc, d_out, st);
+        if (timed) { CU(ctx, cudaEventRecord(ev[5], st)); ctx->n_sub_timed = (int)sb + 1; }
+    }
+    CU(ctx, cudaGetLastError());
+    CU(ctx, cudaMemcpyAsync(ctx->h_cursor, ctx->d_cursor, sizeof(Cursor), cudaMemcpyDeviceToHost, st));
+    return GZB_OK;
+}
+
+void cursor_to_result(const Cursor& c, gzb_result* r)
+{
+    r->in_bytes = c.in_bytes; r->out_bytes = c.out_bytes; r->crc32 = c.crc;
+    r->n_chunks = c.n_chunks; r->n_blocks = c.n_blocks; r->status = c.status;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gzb_deflate_device_async(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
+                             uint8_t* d_out, uint64_t out_cap, void* stream)
+{
+    if (!ctx) return GZB_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    int rc = enqueue_deflate(ctx, level, flags, d_in, n, halo, d_out, out_cap, st);
+    if (rc == GZB_OK) { ctx->pending = true; ctx->pending_n = n; ctx->pending_stream = st; }
+    return rc;
+}
+
+int gzb_deflate_wait(gzb_ctx* ctx, gzb_result* result)
+{
+    if (!ctx) return GZB_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    if (!ctx->pending) return fail(ctx, GZB_E_ARG, "nothing pending");
+    ctx->pending = false;
+    CU(ctx, cudaSetDevice(ctx->device));
+    CU(ctx, cudaStreamSynchronize(ctx->pending_stream));
+    if (ctx->h_cursor->in_bytes != ctx->pending_n) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
+    if (result) cursor_to_result(*ctx->h_cursor, result);
+    return ctx->h_cursor->status;
+}
+
+int gzb_deflate_device(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
+                       uint8_t* d_out, uint64_t out_cap, gzb_result* result, void* stream)
+{
+    int rc = gzb_deflate_device_async(ctx, level, flags, d_in, n, halo, d_out, out_cap, stream);
+    if (rc != GZB_OK) return rc;
+    return gzb_deflate_wait(ctx, result);
+}
+
+int gzb_last_stage_ms(gzb_ctx* ctx, gzb_stage_ms* ms)
+{
+    if (!ctx || !ms) return GZB_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    memset(ms, 0, sizeof(*ms));
+    for (int i = 0; i < ctx->n_sub_timed; i++) {
+        float t[5];
+        for (int j = 0; j < 5; j++) CU(ctx, cudaEventElapsedTime(&t[j], ctx->ev[i][j], ctx->ev[i][j + 1]));
+        ms->crc += t[0]; ms->lz77 += t[1]; ms->huffman += t[2]; ms->layout += t[3]; ms->pack += t[4];
+    }
+    ms->total = ms->crc + ms->lz77 + ms->huffman + ms->layout + ms->pack;
+    return GZB_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// host-buffer path, CRC entry points, gzip framing
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+int ensure_stage(gzb_ctx* ctx, uint64_t in_cap, uint64_t out_cap)
+{
+    if (ctx->stage_in_cap < in_cap) {
+        cudaFree(ctx->d_in); if (ctx->h_in) cudaFreeHost(ctx->h_in);
+        ctx->d_in = nullptr; ctx->h_in = nullptr; ctx->stage_in_cap = 0;
+        cudaError_t e;
+        if ((e = cudaMalloc(&ctx->d_in, in_cap)) != cudaSuccess || (e = cudaMallocHost(&ctx->h_in, in_cap)) != cudaSuccess) {
+            (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "staging (in)", e);
+        }
+        ctx->stage_in_cap = in_cap;
+    }
+    if (ctx->stage_out_cap < out_cap) {
+        cudaFree(ctx->d_out); if (ctx->h_out) cudaFreeHost(ctx->h_out);
+        ctx->d_out = nullptr; ctx->h_out = nullptr; ctx->stage_out_cap = 0;
+        cudaError_t e;
+        if ((e = cudaMalloc(&ctx->d_out, out_cap)) != cudaSuccess || (e = cudaMallocHost(&ctx->h_out, out_cap)) != cudaSuccess) {
+            (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "staging (out)", e);
+        }
+        ctx->stage_out_cap = out_cap;
+    }
+    return GZB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Batches of HOST_BATCH bytes go through pinned staging: memcpy -> H2D -> kernels -> D2H -> memcpy.
+// (Round 1: one staging slot, copies and kernels serialised on the context's stream; the
+// double-buffered version is the next step -- DESIGN.md "Host path".)
+int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in, uint64_t n, const uint8_t* dict,
+                     uint8_t* out, uint64_t out_cap, gzb_result* result)
+{
+    if (!ctx || (n && !in) || !out) return GZB_E_ARG;
+    if (level < 1 || level > 9) return fail(ctx, GZB_E_LEVEL, "level must be 1..9");
+    if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
+    const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
+    const uint32_t chunk = rs ? GZB_RSYNC_CHUNK : GZB_CHUNK, dsz = rs ? 0u : GZB_DICT;
+    const uint64_t HOST_BATCH = 256ull << 20;                      // multiple of both chunk sizes
+    gzb_result total; memset(&total, 0, sizeof(total));
+    uint64_t opos = 0;
+    {
+        std::lock_guard<std::mutex> g(ctx->mu);
+        CU(ctx, cudaSetDevice(ctx->device));
+        uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;
+        int rc = ensure_stage(ctx, dsz + bmax + 16, gzb_bound(bmax, flags));
+        if (rc != GZB_OK) return rc;
+    }
+    uint64_t off = 0;
+    do {
+        const uint64_t nb = (n - off) < HOST_BATCH ? (n - off) : HOST_BATCH;
+        const bool lastb = off + nb == n;
+        // the 32 KiB before this batch: caller's dict for the first batch, the input itself afterwards
+        const uint8_t* halo_src = (off == 0) ? dict : in + off - dsz;
+        const uint32_t halo = (halo_src && dsz) ? dsz : 0u;
+        const uint32_t f = (flags & ~GZB_F_FINAL) | ((lastb && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
+        gzb_result r;
+        {
+            std::lock_guard<std::mutex> g(ctx->mu);
+            uint8_t* hin = ctx->h_in + (dsz - halo);               // keeps d_in + dsz 16-byte aligned
+            if (halo) memcpy(hin, halo_src, halo);
+            if (nb) memcpy(hin + halo, in + off, nb);
+            CU(ctx, cudaMemcpyAsync(ctx->d_in + (dsz - halo), hin, halo + nb, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        int rc = gzb_deflate_device(ctx, level, f, ctx->d_in + dsz, nb, halo, ctx->d_out, ctx->stage_out_cap, &r, ctx->stream);
+        if (rc != GZB_OK) return rc;
+        {
+            std::lock_guard<std::mutex> g(ctx->mu);
+            if (opos + r.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
+            CU(ctx, cudaMemcpyAsync(ctx->h_out, ctx->d_out, r.out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+            CU(ctx, cudaStreamSynchronize(ctx->stream));
+            memcpy(out + opos, ctx->h_out, r.out_bytes);
+        }
+        opos += r.out_bytes;
+        total.crc32 = gzb_crc32_combine(total.crc32, r.crc32, nb);
+        total.in_bytes += nb; total.n_chunks += r.n_chunks; total.n_blocks += r.n_blocks;
+        off += nb;
+        (void)chunk;
+    } while (off < n);
+    total.out_bytes = opos; total.status = GZB_OK;
+    if (result) *result = total;
+    return GZB_OK;
+}
+
+int gzb_crc32_device(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, uint64_t n, uint32_t* crc_out, void* stream)
+{
+    if (!ctx || !crc_out || (n && !d_in)) return GZB_E_ARG;
+    if ((uintptr_t)d_in & 15u) return fail(ctx, GZB_E_ARG, "d_in must be 16-byte aligned");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    const uint32_t chunk = GZB_CHUNK;
+    uint32_t acc = crc;
+    const uint64_t nchunks64 = (n + chunk - 1) / chunk;
+    const uint64_t sub = nchunks64 < 65536 ? nchunks64 : 65536;
+    ChunkRec* d_recs = nullptr; ChunkRec* h_recs = nullptr;
+    if (n) {
+        CU(ctx, cudaMalloc(&d_recs, sizeof(ChunkRec) * sub));
+        h_recs = (ChunkRec*)malloc(sizeof(ChunkRec) * sub);
+        if (!h_recs) { cudaFree(d_recs); return fail(ctx, GZB_E_NOMEM, "malloc"); }
+    }
+    for (uint64_t c0 = 0; c0 < nchunks64; c0 += sub) {
+        const uint32_t nch = (uint32_t)((nchunks64 - c0) < sub ? (nchunks64 - c0) : sub);
+        const uint64_t off = c0 * chunk, nb = (n - off) < (uint64_t)nch * chunk ? (n - off) : (uint64_t)nch * chunk;
+        launch_crc32(d_in + off, nb, chunk, nch, d_recs, ctx->d_tab, st);
+        cudaError_t e = cudaMemcpyAsync(h_recs, d_recs, sizeof(ChunkRec) * nch, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { cudaFree(d_recs); free(h_recs); return fail(ctx, GZB_E_CUDA, "crc32", e); }
+        for (uint32_t i = 0; i < nch; i++) {
+            uint64_t len = (uint64_t)(i + 1) * chunk <= nb ? chunk : nb - (uint64_t)i * chunk;
+            acc = crc_shift(ctx->h_x2n, acc, len) ^ h_recs[i].crc;
+        }
+    }
+    cudaFree(d_recs); free(h_recs);
+    *crc_out = acc;
+    return GZB_OK;
+}
+
+int gzb_crc32_host(gzb_ctx* ctx, uint32_t crc, const uint8_t* in, uint64_t n, uint32_t* crc_out)
+{
+    if (!ctx || !crc_out || (n && !in)) return GZB_E_ARG;
+    const uint64_t B = 256ull << 20;
+    uint32_t acc = crc;
+    for (uint64_t off = 0; off < n; off += B) {
+        const uint64_t nb = (n - off) < B ? (n - off) : B;
+        {
+            std::lock_guard<std::mutex> g(ctx->mu);
+            CU(ctx, cudaSetDevice(ctx->device));
+            int rc = ensure_stage(ctx, GZB_DICT + nb + 16, 0);
+            if (rc != GZB_OK) return rc;
+            memcpy(ctx->h_in, in + off, nb);
+            CU(ctx, cudaMemcpyAsync(ctx->d_in, ctx->h_in, nb, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        int rc = gzb_crc32_device(ctx, acc, ctx->d_in, nb, &acc, ctx->stream);
+        if (rc != GZB_OK) return rc;
+    }
+    *crc_out = acc;
+    return GZB_OK;
+}
+
+uint32_t gzb_crc32_combine(uint32_t crc1, uint32_t crc2, uint64_t len2)
+{
+    static uint32_t x2n[64];
+    static std::once_flag once;
+    std::call_once(once, [] { uint32_t t[CRC_TAB_WORDS]; build_crc_tables(t); memcpy(x2n, t + 1024, sizeof(x2n)); });
+    return crc_shift(x2n, crc1, len2) ^ crc2;
+}
+
+int gzb_gzip_header(int level, uint32_t mtime, const char* name, uint8_t* out, size_t cap)
+{
+    const size_t nl = name ? strlen(name) + 1 : 0;
+    if (!out || cap < 10 + nl) return GZB_E_ARG;
+    out[0] = 0x1f; out[1] = 0x8b; out[2] = 8; out[3] = name ? 8 : 0;
+    out[4] = (uint8_t)mtime; out[5] = (uint8_t)(mtime >> 8); out[6] = (uint8_t)(mtime >> 16); out[7] = (uint8_t)(mtime >> 24);
+    out[8] = (uint8_t)(level >= 9 ? 2 : level == 1 ? 4 : 0);     // XFL, src/parallel.c:43
+    out[9] = 3;                                                    // OS = Unix
+    if (name) memcpy(out + 10, name, nl);
+    return (int)(10 + nl);
+}
+
+int gzb_gzip_trailer(uint32_t crc32, uint64_t isize, uint8_t* out, size_t cap)
+{
+    if (!out || cap < 8) return GZB_E_ARG;
+    const uint32_t sz = (uint32_t)isize;                           // mod 2^32, src/parallel.c:60
+    for (int i = 0; i < 4; i++) { out[i] = (uint8_t)(crc32 >> (8 * i)); out[4 + i] = (uint8_t)(sz >> (8 * i)); }
+    return 8;
+}
+
+}  // extern "C"

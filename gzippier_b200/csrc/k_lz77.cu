@@ -27,7 +27,6 @@ namespace gzb {
 namespace {
 
 constexpr uint32_t FULL = 0xFFFFFFFFu;
-constexpr int NWARPS = LZ_THREADS / 32;
 constexpr int GROUPS_PER_TILE = TILE / 32;
 constexpr int MRING = 2 * TILE;           // per-position match results kept for two tiles
 

@@ -78,8 +78,9 @@ k_pack(const uint8_t* __restrict__ in, uint32_t chunk, const uint32_t* __restric
             }
             if (tid < 8u) {
                 // head bytes [dbyte, wfirst*4) and tail bytes [max(wlast*4, dbyte), dend)
-                uint64_t pos = (tid < 4u) ? dbyte + tid : max(wlast * 4ull, dbyte) + (tid - 4u);
-                bool ok = (tid < 4u) ? (pos < min(wfirst * 4ull, dend)) : (pos < dend && wlast >= wfirst);
+                const uint64_t wl4 = wlast * 4ull, wf4 = wfirst * 4ull;
+                uint64_t pos = (tid < 4u) ? dbyte + tid : (wl4 > dbyte ? wl4 : dbyte) + (tid - 4u);
+                bool ok = (tid < 4u) ? (pos < (wf4 < dend ? wf4 : dend)) : (pos < dend && wlast >= wfirst);
                 if (ok) atomicOr(&out32[pos >> 2], (uint32_t)src[off + (pos - dbyte)] << ((pos & 3ull) * 8ull));
             }
             bit = (dbyte + len) * 8ull;

@@ -53,9 +53,9 @@ void gzm_level_params(int level, gzm_params *p)
 {
     static const struct { int good, lazy, nice, chain, depth; } t[10] = {
         {0, 0, 0, 0, 0},
-        {4, 4, 8, 4, 2}, {4, 5, 16, 8, 3}, {4, 6, 32, 32, 6},
-        {4, 4, 16, 16, 8}, {8, 16, 32, 32, 12}, {8, 16, 128, 128, 24},
-        {8, 32, 128, 256, 32}, {32, 128, 258, 1024, 48}, {32, 258, 258, 4096, 96}};
+        {4, 4, 8, 4, 1}, {4, 5, 16, 8, 2}, {4, 6, 32, 32, 4},
+        {4, 4, 16, 16, 8}, {8, 16, 32, 32, 16}, {8, 16, 128, 128, 32},
+        {8, 32, 128, 256, 40}, {32, 128, 258, 1024, 64}, {32, 258, 258, 4096, 96}};
     memset(p, 0, sizeof(*p));
     p->level = level;
     p->good = t[level].good; p->max_lazy = t[level].lazy; p->nice = t[level].nice;
@@ -66,7 +66,6 @@ void gzm_level_params(int level, gzm_params *p)
 }
 
 /* ---------------- match finder ---------------- */
-uint64_t gzm_ctr_cand = 0, gzm_ctr_groupmax = 0, gzm_ctr_full = 0, gzm_ctr_pos = 0;   /* instrumentation (not thread-safe: explore with 1 thread) */
 static inline uint32_t ld32(const uint8_t *p) { uint32_t v; memcpy(&v, p, 4); return v; }
 uint32_t gzm_hash4(uint32_t v, int hbits) { return (v * 0x9E3779B1u) >> (32 - hbits); }
 uint32_t gzm_hash3(uint32_t v) { return ((v << 8) * 0x9E3779B1u) >> (32 - GZM_H3BITS); }
@@ -95,17 +94,15 @@ void gzm_find_matches(const gzm_params *P, const uint8_t *s, int D, int n, uint1
         int best = 2, bdist = 0;
         int limit = p < P->maxd ? p : P->maxd;
         int nice = P->nice < maxlen ? P->nice : maxlen;
-        int c = link[p], depth = P->depth; int ncand = 0; static __thread int gmax = 0;
+        int c = link[p], depth = P->depth;
         while (c >= 0 && p - c <= limit && depth-- > 0) {
-            ncand++;
             if (maxlen > best && s[c + best] == s[p + best]) {
-                int l = 0; gzm_ctr_full++;
+                int l = 0;
                 while (l < maxlen && s[c + l] == s[p + l]) l++;
                 if (l > best) { best = l; bdist = p - c; if (l >= nice) break; }
             }
             c = link[c];
         }
-        gzm_ctr_cand += ncand; gzm_ctr_pos++; if (ncand > gmax) gmax = ncand; if ((p & 31) == 31) { gzm_ctr_groupmax += gmax; gmax = 0; }
         /* no match of 4+ on the chain: try the most recent 3-byte twin (single-entry table) */
         if (best < 3 && P->use_h3 && prev3 >= 0 && p - prev3 <= (limit < GZM_TOO_FAR ? limit : GZM_TOO_FAR) && maxlen >= 3) {
             int l = 0;
