@@ -309,6 +309,16 @@ int gzb_deflate_device(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d
     return gzb_deflate_wait(ctx, result);
 }
 
+// debugging aid (not in gzb200.h): cycle counters of k_lz77's pipeline phases, see k_lz77.cu
+int gzb_debug_lzprof(gzb_ctx* ctx, unsigned long long* out16, int reset)
+{
+    if (!ctx || !out16) return GZB_E_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    CU(ctx, cudaDeviceSynchronize());
+    CU(ctx, lz77_read_prof(out16, reset));
+    return GZB_OK;
+}
+
 int gzb_last_stage_ms(gzb_ctx* ctx, gzb_stage_ms* ms)
 {
     if (!ctx || !ms) return GZB_E_ARG;

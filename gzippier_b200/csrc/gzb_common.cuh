@@ -160,5 +160,6 @@ void launch_layout(BlockRec* blocks, ChunkRec* chunks, uint32_t nchunks, uint32_
 void launch_pack(const uint8_t* in, uint32_t chunk, const uint32_t* tokens, const BlockRec* blocks, const ChunkRec* chunks,
                  uint32_t nchunks, uint32_t bpc, uint8_t* out, cudaStream_t st);
 cudaError_t lz77_configure();
+cudaError_t lz77_read_prof(unsigned long long* out16, int reset);
 
 }  // namespace gzb

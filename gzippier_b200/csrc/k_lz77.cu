@@ -24,6 +24,10 @@
 
 namespace gzb {
 
+// cycle counters of the pipeline phases (thread 0 = inserter warp, thread 32 = a searcher warp), summed over CTAs:
+// 0 insert, 1 load, 2 warp0 search, 3 warp0 wait A, 4 walk, 5 emit+syncs, 6 warp1 search, 7 warp1 wait A, 8 chunk setup, 9 tiles
+__device__ unsigned long long g_lzprof[16];
+
 namespace {
 
 constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -253,6 +257,9 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         uint32_t* tok = tokens + (size_t)c * chunk;
         BlockRec* brecs = blocks + (size_t)c * bpc;
 
+        unsigned long long pf[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        long long t0 = clock64(), t1;
+#define PF(i) do { t1 = clock64(); pf[i] += (unsigned long long)(t1 - t0); t0 = t1; } while (0)
         // ---- per-chunk reset ----
         for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = 0;
         for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = 0;
@@ -261,6 +268,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[0] = 0; S.grp_ctr[1] = 0; }
         for (uint32_t t = 0; t < 3; t++) load_tile(S, sp, n_s, t, tid, LZ_THREADS);
         __syncthreads();
+        PF(8);
 
         // ---- pipeline: iteration k inserts tile k+1 while tile k is searched, then parses tile k ----
         for (int k = -1; k < (int)ntiles; k++) {
@@ -269,7 +277,9 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             if (tid == 0) S.grp_ctr[(k + 1) & 1] = 0;           // last used two barriers ago
             if (warp == 0) {
                 if (k + 1 < (int)ntiles) insert_tile(S, (uint32_t)(k + 1), n_s, lane);
+                PF(0);
                 load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
+                PF(1);
             }
             const bool ctile = k >= (int)first_ctile;
             if (ctile) {
@@ -282,7 +292,10 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     search_group(S, lp, (uint32_t)k, g, n_s, lane);
                 }
             }
+            PF(warp == 0 ? 2 : 6);
             __syncthreads();
+            PF(warp == 0 ? 3 : 7);
+            pf[9]++;
             if (!ctile) continue;                       // uniform: dictionary tiles are insert-only
 
             // stage B: parse tile k.  Decidable positions: [k*TILE-1, hi) (lazy needs mlen[p+1]).
@@ -330,6 +343,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     S.entry = (uint32_t)e; S.extra_lit = extra;
                 }
             }
+            PF(4);
             __syncthreads();
             // emission: 2 positions per thread
             {
@@ -364,6 +378,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             __syncthreads();
             if (tid == 0) { S.ntok += S.seg_prefix[32] + S.extra_lit; S.extra_lit = 0; }
             __syncthreads();
+            PF(5);
         }
 
         // ---- chunk epilogue ----
@@ -371,11 +386,22 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         if (tid == 0) {
             ChunkRec* cr = &chunks[c];
             cr->n_bytes = nc; cr->n_blocks = nblocks; cr->n_tokens = S.ntok;
+            for (int i = 0; i < 6; i++) atomicAdd(&g_lzprof[i], pf[i]);
+            atomicAdd(&g_lzprof[8], pf[8]); atomicAdd(&g_lzprof[9], pf[9]);
         }
+        if (tid == 32) { atomicAdd(&g_lzprof[6], pf[6]); atomicAdd(&g_lzprof[7], pf[7]); }
+#undef PF
     }
 }
 
 }  // namespace
+
+cudaError_t lz77_read_prof(unsigned long long* out16, int reset)
+{
+    cudaError_t e = cudaMemcpyFromSymbol(out16, g_lzprof, sizeof(unsigned long long) * 16);
+    if (e == cudaSuccess && reset) { unsigned long long z[16] = {0}; e = cudaMemcpyToSymbol(g_lzprof, z, sizeof(z)); }
+    return e;
+}
 
 cudaError_t lz77_configure()
 {
