@@ -103,41 +103,54 @@ __device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n
     }
 }
 
-// Insert the positions of tile t into the chain table and the 3-byte table, in stream order.
-// One warp; 32 consecutive positions per step; duplicates inside a step are linked by lane order.
+// Insert the positions of tile t into one hash table, in stream order.  One warp; 32 consecutive
+// positions per step.  CHAIN: 4-byte buckets, result = link delta per position (S.link);
+// otherwise 3-byte buckets, result = delta to the most recent twin within TOO_FAR (S.c3).
+// Every lane reads the bucket head, then all lanes write their position and read it back: a lane
+// that does not find its own position shares its bucket with another lane of the same step
+// (MATCH.ANY would tell the same, at ~500 cycles per step when the 32 values are distinct);
+// only those rare groups are then ordered by lane with ballots.
+template <bool CHAIN>
 __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane)
 {
-    uint32_t base = t * TILE;
-    uint32_t slot = base % LINK_RING + lane;
+    const uint32_t base = t * TILE;
+    uint16_t* table = CHAIN ? S.head : S.head3;
     uint16_t* c3 = S.c3[t & 1];
+    uint32_t slot = base % LINK_RING + lane;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t v = ring_ld32(S.ring32, base + lane);
     for (uint32_t i = 0; i < GROUPS_PER_TILE; i++, slot += 32) {
-        uint32_t p = base + i * 32u + lane;
+        const uint32_t p = base + i * 32u + lane;
         if (base + i * 32u >= n_s) break;                       // nothing past the end is ever searched
         if (slot >= LINK_RING) slot -= LINK_RING;
-        uint32_t v = ring_ld32(S.ring32, p);
-        uint32_t h = hash4(v), h3 = hash3(v);
-        // 4-byte chains
-        uint32_t peers = __match_any_sync(FULL, h);
-        uint32_t lower = peers & ((1u << lane) - 1u);
+        const uint32_t h = CHAIN ? hash4(v) : hash3(v);
+        const uint32_t old = table[h];
+        // candidate = bucket head as of the previous step; fetch its bytes now, judge them later
+        const uint32_t d = (p - old) & 0xFFFFu;
+        const bool in_range = d != 0u && d <= (CHAIN ? 32767u : (uint32_t)TOO_FAR) && d <= p;
+        const uint32_t cv = ring_ld32(S.ring32, in_range ? p - d : p);
+        __syncwarp();
+        table[h] = (uint16_t)p;
+        __syncwarp();
+        const uint32_t won = table[h];
+        v = ring_ld32(S.ring32, p + 32u);                       // next step's bytes (ring is read-only here)
+        uint32_t todo = __ballot_sync(FULL, won != (p & 0xFFFFu));
+        int lower_lane = -1;
+        while (todo) {                                          // uniform; rare
+            const int leader = __ffs(todo) - 1;
+            const uint32_t hv = __shfl_sync(FULL, h, leader);
+            const uint32_t grp = __ballot_sync(FULL, h == hv);
+            if (h == hv) {
+                const uint32_t lower = grp & lt_mask;
+                if (lower) lower_lane = 31 - __clz(lower);
+                if ((grp >> lane) == 1u) table[h] = (uint16_t)p;    // the last position of the step owns the bucket
+            }
+            todo &= ~grp;
+        }
         uint32_t delta = 0;
-        if (lower) delta = lane - (31u - __clz(lower));
-        else {
-            uint32_t d = (p - (uint32_t)S.head[h]) & 0xFFFFu;
-            if (d != 0u && d <= 32767u && d <= p && hash4(ring_ld32(S.ring32, p - d)) == h) delta = d;
-        }
-        S.link[slot] = (uint16_t)delta;
-        if ((peers >> lane) == 1u) S.head[h] = (uint16_t)p;
-        // 3-byte single-entry table
-        uint32_t peers3 = __match_any_sync(FULL, h3);
-        uint32_t lower3 = peers3 & ((1u << lane) - 1u);
-        uint32_t d3 = 0;
-        if (lower3) d3 = lane - (31u - __clz(lower3));
-        else {
-            uint32_t d = (p - (uint32_t)S.head3[h3]) & 0xFFFFu;
-            if (d != 0u && d <= (uint32_t)TOO_FAR && d <= p && hash3(ring_ld32(S.ring32, p - d)) == h3) d3 = d;
-        }
-        c3[i * 32u + lane] = (uint16_t)d3;
-        if ((peers3 >> lane) == 1u) S.head3[h3] = (uint16_t)p;
+        if (lower_lane >= 0) delta = lane - (uint32_t)lower_lane;
+        else if (in_range && (CHAIN ? hash4(cv) : hash3(cv)) == h) delta = d;     // stale/aliased heads fail the re-hash
+        if (CHAIN) S.link[slot] = (uint16_t)delta; else c3[i * 32u + lane] = (uint16_t)delta;
         __syncwarp();
     }
 }
@@ -257,7 +270,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         uint32_t* tok = tokens + (size_t)c * chunk;
         BlockRec* brecs = blocks + (size_t)c * bpc;
 
-        unsigned long long pf[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        unsigned long long pf[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pf31 = 0;
         long long t0 = clock64(), t1;
 #define PF(i) do { t1 = clock64(); pf[i] += (unsigned long long)(t1 - t0); t0 = t1; } while (0)
         // ---- per-chunk reset ----
@@ -275,11 +288,13 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             // stage A
             uint32_t* gctr = &S.grp_ctr[k & 1];
             if (tid == 0) S.grp_ctr[(k + 1) & 1] = 0;           // last used two barriers ago
-            if (warp == 0) {
-                if (k + 1 < (int)ntiles) insert_tile(S, (uint32_t)(k + 1), n_s, lane);
-                PF(0);
+            // the SMSP arbiter favours the highest warp ids: give them the two serial inserter roles
+            if (warp == 31) {
+                if (k + 1 < (int)ntiles) insert_tile<true>(S, (uint32_t)(k + 1), n_s, lane);
+                if (lane == 0) pf31 += (unsigned long long)(clock64() - t0);
+            } else if (warp == 30) {
+                if (k + 1 < (int)ntiles) insert_tile<false>(S, (uint32_t)(k + 1), n_s, lane);
                 load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
-                PF(1);
             }
             const bool ctile = k >= (int)first_ctile;
             if (ctile) {
@@ -292,7 +307,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     search_group(S, lp, (uint32_t)k, g, n_s, lane);
                 }
             }
-            PF(warp == 0 ? 2 : 6);
+            PF(warp == 0 ? 2 : 6);   // warp 2 (thread 64) is a pure searcher
             __syncthreads();
             PF(warp == 0 ? 3 : 7);
             pf[9]++;
@@ -389,7 +404,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             for (int i = 0; i < 6; i++) atomicAdd(&g_lzprof[i], pf[i]);
             atomicAdd(&g_lzprof[8], pf[8]); atomicAdd(&g_lzprof[9], pf[9]);
         }
-        if (tid == 32) { atomicAdd(&g_lzprof[6], pf[6]); atomicAdd(&g_lzprof[7], pf[7]); }
+        if (tid == 64) { atomicAdd(&g_lzprof[6], pf[6]); atomicAdd(&g_lzprof[7], pf[7]); }
+        if (tid == 31 * 32) atomicAdd(&g_lzprof[0], pf31);
 #undef PF
     }
 }
