@@ -32,10 +32,11 @@ namespace {
 
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 constexpr int GROUPS_PER_TILE = TILE / 32;
+constexpr int RING_MIRROR = 272;         // >= 258 + 3 (longest compare) + 4, multiple of 16
 constexpr int MRING = 2 * TILE;           // per-position match results kept for two tiles
 
 struct Smem {
-    uint32_t ring32[RING / 4];
+    uint32_t ring32[RING / 4 + RING_MIRROR / 4];   // + mirror of the first bytes: compare loops never wrap
     uint16_t link[LINK_RING];
     uint16_t head[1 << HBITS];
     uint16_t head3[1 << H3BITS];
@@ -59,7 +60,7 @@ struct Smem {
 __device__ __forceinline__ uint32_t ring_ld32(const uint32_t* ring32, uint32_t pos)
 {
     uint32_t a = pos & 0xFFFFu, i = a >> 2;
-    uint32_t w0 = ring32[i], w1 = ring32[(i + 1) & (RING / 4 - 1)];
+    uint32_t w0 = ring32[i], w1 = ring32[i + 1];               // i + 1 may be the mirror
     return __funnelshift_r(w0, w1, (a & 3u) * 8u);
 }
 __device__ __forceinline__ uint32_t ring_ld8(const uint32_t* ring32, uint32_t pos)
@@ -67,22 +68,22 @@ __device__ __forceinline__ uint32_t ring_ld8(const uint32_t* ring32, uint32_t po
     return reinterpret_cast<const uint8_t*>(ring32)[pos & 0xFFFFu];
 }
 
-// length of the common prefix of the strings at stream positions p and c, at most maxlen
+// length of the common prefix of the strings at stream positions p and c, at most maxlen (>= 1)
 __device__ __forceinline__ int match_len(const uint32_t* ring32, uint32_t p, uint32_t c, int maxlen)
 {
-    uint32_t ap = p & 0xFFFFu, ac = c & 0xFFFFu;
-    uint32_t ip = ap >> 2, ic = ac >> 2, sp = (ap & 3u) * 8u, sc = (ac & 3u) * 8u;
-    uint32_t p0 = ring32[ip], c0 = ring32[ic];
-    int l = 0;
-    while (l + 4 <= maxlen) {
-        ip = (ip + 1) & (RING / 4 - 1); ic = (ic + 1) & (RING / 4 - 1);
-        uint32_t p1 = ring32[ip], c1 = ring32[ic];
-        uint32_t x = __funnelshift_r(p0, p1, sp) ^ __funnelshift_r(c0, c1, sc);
-        if (x) return l + ((__ffs(x) - 1) >> 3);
-        l += 4; p0 = p1; c0 = c1;
+    const uint32_t ap = p & 0xFFFFu, ac = c & 0xFFFFu;
+    const uint32_t* wp = ring32 + (ap >> 2);
+    const uint32_t* wc = ring32 + (ac >> 2);
+    const uint32_t sp = (ap & 3u) * 8u, sc = (ac & 3u) * 8u;
+    uint32_t p0 = wp[0], c0 = wc[0];
+    const int nw = (maxlen + 3) >> 2;
+    for (int k = 1; k <= nw; k++) {
+        const uint32_t p1 = wp[k], c1 = wc[k];
+        const uint32_t x = __funnelshift_r(p0, p1, sp) ^ __funnelshift_r(c0, c1, sc);
+        if (x) return min(maxlen, 4 * (k - 1) + ((__ffs(x) - 1) >> 3));
+        p0 = p1; c0 = c1;
     }
-    while (l < maxlen && ring_ld8(ring32, p + l) == ring_ld8(ring32, c + l)) l++;
-    return l;
+    return maxlen;
 }
 
 // Copy stream bytes [t*TILE, (t+1)*TILE) into the ring, zero beyond the end of the stream.
@@ -99,7 +100,9 @@ __device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n
             for (uint32_t k = 0; pos + k < n_s; k++) w[k >> 2] |= (uint32_t)sp[pos + k] << ((k & 3u) * 8u);
             v = make_uint4(w[0], w[1], w[2], w[3]);
         }
-        *reinterpret_cast<uint4*>(&S.ring32[(pos & 0xFFFFu) >> 2]) = v;
+        const uint32_t ra = pos & 0xFFFFu;
+        *reinterpret_cast<uint4*>(&S.ring32[ra >> 2]) = v;
+        if (ra < (uint32_t)RING_MIRROR) *reinterpret_cast<uint4*>(&S.ring32[(RING + ra) >> 2]) = v;
     }
 }
 
@@ -161,30 +164,56 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
     uint32_t p = t * TILE + g * 32u + lane;
     int maxlen = (p < n_s) ? min(258, (int)(n_s - p)) : 0;
     int best = 2; uint32_t bdist = 0;
-    if (maxlen >= 3) {
-        uint32_t limit = min((uint32_t)MAXD, p);
-        int nice = min(lp.nice, maxlen);
-        int32_t slot = (int32_t)(p % LINK_RING);
-        uint32_t delta = S.link[slot];
-        uint32_t d = 0;
-        int depth = lp.depth;
-        uint32_t scan_end = ring_ld8(S.ring32, p + best);
-        while (delta != 0u && depth > 0) {
-            d += delta;
-            if (d > limit) break;
-            depth--;
-            uint32_t c = p - d;
-            slot -= (int32_t)delta; if (slot < 0) slot += LINK_RING;
-            if (best < maxlen && ring_ld8(S.ring32, c + best) == scan_end) {
-                int l = match_len(S.ring32, p, c, maxlen);
-                if (l > best) {
-                    best = l; bdist = d;
-                    if (l >= nice) break;
-                    scan_end = ring_ld8(S.ring32, p + best);
+    // The chain walk alternates two converged phases:
+    //   A: WALK_STEPS lockstep chain steps; a candidate that passes the one-byte filter is only noted
+    //      (up to two per lane; a lane with two noted candidates sits out the rest of the phase)
+    //   B: the noted candidates are measured, first noted first, by all lanes that hold one
+    // Filtering in A uses the best length as of the last B, which is a weaker (still necessary)
+    // condition; B re-applies the exact filter.  Candidates are judged in chain order with the
+    // "strictly longer wins" rule, so the result equals the one-candidate-at-a-time walk.
+    constexpr int WALK_STEPS = 8;
+    uint32_t limit = min((uint32_t)MAXD, p);
+    bool active = maxlen >= 3;
+    int nice = min(lp.nice, maxlen);
+    int32_t slot = (int32_t)(p % LINK_RING);
+    uint32_t delta = active ? (uint32_t)S.link[slot] : 0u;
+    uint32_t d = 0;
+    int depth = lp.depth;
+    uint32_t scan_end = ring_ld8(S.ring32, p + best);
+    while (__any_sync(FULL, active)) {
+        uint32_t pend0 = 0, pend1 = 0;
+#pragma unroll 1
+        for (int st = 0; st < WALK_STEPS; st++) {
+            if (active && pend1 == 0u) {
+                if (delta == 0u || depth == 0) active = false;
+                else {
+                    d += delta;
+                    if (d > limit) active = false;
+                    else {
+                        depth--;
+                        slot -= (int32_t)delta; if (slot < 0) slot += LINK_RING;
+                        const bool pass = ring_ld8(S.ring32, p - d + best) == scan_end;
+                        delta = S.link[slot];
+                        if (pass) { if (pend0) pend1 = d; else pend0 = d; }
+                    }
                 }
             }
-            delta = S.link[slot];
         }
+        bool done = false;
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const uint32_t cand = r ? pend1 : pend0;
+            if (cand && !done && ring_ld8(S.ring32, p - cand + best) == scan_end) {
+                int l = match_len(S.ring32, p, p - cand, maxlen);
+                if (l > best) {
+                    best = l; bdist = cand;
+                    if (l >= nice || l >= maxlen) { done = true; active = false; }
+                    else scan_end = ring_ld8(S.ring32, p + best);
+                }
+            }
+        }
+    }
+    if (maxlen >= 3) {
         if (best < 3 && lp.use_h3) {
             uint32_t d3 = S.c3[t & 1][g * 32u + lane];
             if (d3 != 0u && d3 <= min(limit, (uint32_t)TOO_FAR)) {
