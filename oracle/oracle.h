@@ -28,11 +28,9 @@ size_t   orc_gzip_trailer(uint32_t crc, uint64_t ulen, uint8_t *out);       /* s
 typedef struct orc_inflate_stats { uint64_t blocks[3], literals, matches, out_bytes, in_bits; int bfinal_seen; } orc_inflate_stats;
 int64_t  orc_inflate(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, orc_inflate_stats *st);
 
-/* deflate_oracle.c -- the reference's deflate (zlib 1.2.11 deflate_fast/deflate_slow + trees) */
-int64_t  orc_deflate_raw(int level, const uint8_t *dict, size_t dict_len, const uint8_t *in, size_t n,
-                         int last, uint8_t *out, size_t out_cap);
-int64_t  orc_parallel_gzip(int level, const uint8_t *in, size_t n, uint8_t *out, size_t out_cap, int nthreads);
-int64_t  orc_single_gzip(int level, const uint8_t *in, size_t n, uint8_t *out, size_t out_cap);
+/* The deflate arithmetic itself (lib/zlib deflate.c/trees.c) is exercised through oracle/_ref -- the
+ * reference's own sources compiled by oracle/Makefile -- and through the sizes frozen from it in
+ * tests/golden/; engine_model.[ch] is the CPU statement of the ENGINE's algorithm, not the reference's. */
 
 #ifdef __cplusplus
 }
