@@ -1,0 +1,46 @@
+"""The engine's CPU model (oracle/engine_model.c -- the executable spec the CUDA kernels are compared with byte for
+byte on the GPU box) must itself satisfy the parity contract: zlib decodes it, and its size stays within 3 % of the
+reference at the same level (sizes frozen from the reference in tests/golden/)."""
+import zlib
+import pytest
+from conftest import EDGE_SIZES
+
+
+@pytest.mark.parametrize("kind", ["text", "zipf", "binary", "mixed", "random"])
+def test_model_ratio_within_3pct_of_reference(gz, orc, golden, kind):
+    e = golden["corpora"][kind]
+    d = gz.corpus(kind, e["n"], seed=golden["seed"])
+    for level in (1, 2, 3, 4, 5, 6, 7, 8, 9):
+        raw = orc.engine_model(d, level)
+        assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+        ref_body = e["parallel"][str(level)]["size"] - 18
+        assert raw.size <= 1.03 * ref_body, (kind, level, raw.size, ref_body)
+
+
+@pytest.mark.parametrize("n", EDGE_SIZES)
+def test_model_edge_sizes(gz, orc, n):
+    d = gz.corpus("text", n, seed=3)
+    for level in (1, 6):
+        raw = orc.engine_model(d, level)
+        assert orc.inflate(raw, n).tobytes() == d.tobytes()
+        assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+
+
+def test_model_fragments_are_byte_aligned_and_independent_of_the_cut(gz, orc):
+    # chunk grid semantics of parallel.c: compressing [0,n) in one call equals compressing two shards with a 32 KiB halo
+    n = 5 * 131072 + 4321
+    d = gz.corpus("zipf", n, seed=11)
+    whole = orc.engine_model(d, 6).tobytes()
+    cut = 3 * 131072
+    a = orc.engine_model(d[:cut].copy(), 6, final=False).tobytes()
+    b = orc.engine_model(d, 6, halo=32768, skip=cut).tobytes()
+    assert a + b == whole
+    assert zlib.decompress(a + b, -15) == d.tobytes()
+
+
+def test_model_rsyncable(gz, orc, golden):
+    e = golden["corpora"]["text"]
+    d = gz.corpus("text", e["n"], seed=golden["seed"])
+    raw = orc.engine_model(d, 6, rsyncable=True)
+    assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+    assert raw.size <= 1.03 * (e["rsyncable_parallel_6"] - 18)
