@@ -45,8 +45,9 @@ struct Smem {
     uint8_t  mlen[MRING];                 // len-3
     uint32_t lfreq[288];
     uint32_t dfreq[32];
-    unsigned long long masks[32];         // token-start bitmap of the tile being parsed
-    uint32_t seg_prefix[33];
+    uint32_t masks[TILE / 32];            // token-start bitmap of the tile being parsed
+    uint32_t seg_prefix[TILE / 32 + 1];
+    uint16_t jump[2][TILE];               // pointer doubling: 2^r-th successor of every position (TILE = leaves the tile)
     uint32_t grp_ctr[2];                  // dynamic group scheduler, alternating per pipeline step
     uint32_t chunk_idx;
     uint32_t entry;                       // next token start (stream position)
@@ -242,24 +243,6 @@ __device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams&
     return lit ? 1u : L;
 }
 
-// Walk from `start` inside [seg_lo, seg_hi); stop on leaving the segment or on reaching a position the
-// speculative walk of this segment already visited (then the rest of the path is the speculative one).
-__device__ __forceinline__ void seg_walk(const Smem& S, const LevelParams& lp, uint32_t n_s, int seg_lo, int seg_hi,
-                                         int start, unsigned long long spec_mask, int spec_exit,
-                                         unsigned long long& mask, int& exit_pos)
-{
-    unsigned long long m = 0ull;
-    int p = start;
-    while (p < seg_hi) {
-        unsigned long long bit = 1ull << (p - seg_lo);
-        if (spec_mask & bit) { mask = m | (spec_mask & ~(bit - 1ull)); exit_pos = spec_exit; return; }
-        m |= bit;
-        bool lit;
-        p += (int)parse_step(S, lp, (uint32_t)p, n_s, lit);
-    }
-    mask = m; exit_pos = p;
-}
-
 __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid)
 {
     // histograms of the block that just ended -> global; reset for the next one
@@ -299,7 +282,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         uint32_t* tok = tokens + (size_t)c * chunk;
         BlockRec* brecs = blocks + (size_t)c * bpc;
 
-        unsigned long long pf[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pf31 = 0;
+        unsigned long long pf[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pf31 = 0, pf10 = 0;
         long long t0 = clock64(), t1;
 #define PF(i) do { t1 = clock64(); pf[i] += (unsigned long long)(t1 - t0); t0 = t1; } while (0)
         // ---- per-chunk reset ----
@@ -355,37 +338,62 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 if (tid == 0) { S.blk++; S.blk_tok0 = S.ntok; S.blk_in0 = S.entry - D; }
                 __syncthreads();
             }
-            if (warp == 0) {
-                const int entry = (int)S.entry;                   // >= base by construction
-                const int seg_lo = base + 64 * (int)lane;
-                const int seg_hi = min(seg_lo + 64, hi_w);
-                // speculative walk: lane 0 starts at the true entry, the others at their segment start
-                const int spec_start = (lane == 0) ? entry : seg_lo;
-                unsigned long long spec_mask = 0ull, m = 0ull; int spec_exit = spec_start;
-                if (spec_start < seg_hi) seg_walk(S, lp, n_s, seg_lo, seg_hi, spec_start, 0ull, 0, spec_mask, spec_exit);
-                int x = spec_exit, assumed = -2;
-                for (;;) {
-                    int up = __shfl_up_sync(FULL, x, 1);
-                    int a = (lane == 0) ? entry : up;             // a >= seg_lo: exits never fall short of the next segment
-                    bool redo = (a != assumed);
-                    if (!__any_sync(FULL, redo)) break;
-                    if (redo) {
-                        assumed = a;
-                        if (a >= seg_hi) { m = 0ull; x = a; }
-                        else if (a == spec_start) { m = spec_mask; x = spec_exit; }
-                        else seg_walk(S, lp, n_s, seg_lo, seg_hi, a, spec_mask, spec_exit, m, x);
+            // parse(p) is a pure function of the per-position matches, so the token starts of the tile are the
+            // positions reachable from the entry point along next(): pointer doubling over all positions
+            // (round r marks what is 2^r hops behind a marked position) instead of a serial walk.
+            const int entry = (int)S.entry;                       // >= base by construction
+            const int lim = hi_w - base;                          // positions [0, lim) of the tile can start a token
+            int rawnx[TILE / LZ_THREADS];
+#pragma unroll
+            for (int r = 0; r < TILE / LZ_THREADS; r++) {
+                const int o = (int)tid + r * LZ_THREADS;
+                int nx = TILE;
+                if (o < lim) { bool lit; nx = o + (int)parse_step(S, lp, (uint32_t)(base + o), n_s, lit); }
+                rawnx[r] = nx;
+                S.jump[0][o] = (uint16_t)(nx < lim ? nx : TILE);
+            }
+            if (tid < TILE / 32) S.masks[tid] = (entry - base < lim && (uint32_t)(entry - base) / 32u == tid) ? 1u << ((entry - base) & 31) : 0u;
+            __syncthreads();
+            PF(1);
+            for (int rd = 0;; rd++) {
+                pf10++;
+                const uint16_t* jc = S.jump[rd & 1]; uint16_t* jn = S.jump[(rd + 1) & 1];
+                bool more = false;
+#pragma unroll
+                for (int r = 0; r < TILE / LZ_THREADS; r++) {
+                    const int o = (int)tid + r * LZ_THREADS;
+                    const uint32_t j = jc[o];
+                    uint32_t jj = TILE;
+                    if (j < (uint32_t)TILE) {
+                        if ((S.masks[o >> 5] >> (o & 31)) & 1u) { atomicOr(&S.masks[j >> 5], 1u << (j & 31u)); more = true; }
+                        jj = jc[j];
                     }
+                    jn[o] = (uint16_t)jj;
                 }
-                uint32_t cnt = (uint32_t)__popcll(m), incl = cnt;
-                for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= (uint32_t)o) incl += v; }
-                S.masks[lane] = m;
-                S.seg_prefix[lane] = incl - cnt;
-                if (lane == 31) {
-                    S.seg_prefix[32] = incl;
-                    int e = x; uint32_t extra = 0;
+                if (!__syncthreads_or(more)) break;
+            }
+            // the marked position whose successor leaves the tile carries the entry point of the next tile
+            {
+                int e = -1;
+#pragma unroll
+                for (int r = 0; r < TILE / LZ_THREADS; r++) {
+                    const int o = (int)tid + r * LZ_THREADS;
+                    if (o < lim && rawnx[r] >= lim && ((S.masks[o >> 5] >> (o & 31)) & 1u)) e = base + rawnx[r];
+                }
+                if (entry - base >= lim && tid == 0) e = entry;   // the whole tile lies inside one match
+                if (e >= 0) {
+                    uint32_t extra = 0;
                     if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
                     S.entry = (uint32_t)e; S.extra_lit = extra;
                 }
+            }
+            if (warp == 0) {
+                const uint32_t c0 = (uint32_t)__popc(S.masks[2 * lane]), c1 = (uint32_t)__popc(S.masks[2 * lane + 1]);
+                uint32_t incl = c0 + c1;
+                for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= (uint32_t)o) incl += v; }
+                S.seg_prefix[2 * lane] = incl - c0 - c1;
+                S.seg_prefix[2 * lane + 1] = incl - c1;
+                if (lane == 31) S.seg_prefix[TILE / 32] = incl;
             }
             PF(4);
             __syncthreads();
@@ -395,10 +403,10 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
 #pragma unroll
                 for (int r = 0; r < 2; r++) {
                     uint32_t o = tid * 2u + (uint32_t)r;
-                    uint32_t seg = o >> 6, bit = o & 63u;
-                    unsigned long long mk = S.masks[seg];
-                    if ((mk >> bit) & 1ull) {
-                        uint32_t idx = ntok0 + S.seg_prefix[seg] + (uint32_t)__popcll(mk & ((1ull << bit) - 1ull));
+                    uint32_t seg = o >> 5, bit = o & 31u;
+                    uint32_t mk = S.masks[seg];
+                    if ((mk >> bit) & 1u) {
+                        uint32_t idx = ntok0 + S.seg_prefix[seg] + (uint32_t)__popc(mk & ((1u << bit) - 1u));
                         uint32_t p = (uint32_t)(base + (int)o);
                         bool lit; uint32_t step = parse_step(S, lp, p, n_s, lit);
                         uint32_t tv;
@@ -416,11 +424,11 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     uint32_t p = (uint32_t)(base + TILE);
                     uint32_t tv = ring_ld8(S.ring32, p);
                     atomicAdd(&S.lfreq[tv], 1u);
-                    tok[ntok0 + S.seg_prefix[32]] = tv;
+                    tok[ntok0 + S.seg_prefix[TILE / 32]] = tv;
                 }
             }
             __syncthreads();
-            if (tid == 0) { S.ntok += S.seg_prefix[32] + S.extra_lit; S.extra_lit = 0; }
+            if (tid == 0) { S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0; }
             __syncthreads();
             PF(5);
         }
@@ -431,7 +439,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             ChunkRec* cr = &chunks[c];
             cr->n_bytes = nc; cr->n_blocks = nblocks; cr->n_tokens = S.ntok;
             for (int i = 0; i < 6; i++) atomicAdd(&g_lzprof[i], pf[i]);
-            atomicAdd(&g_lzprof[8], pf[8]); atomicAdd(&g_lzprof[9], pf[9]);
+            atomicAdd(&g_lzprof[8], pf[8]); atomicAdd(&g_lzprof[9], pf[9]); atomicAdd(&g_lzprof[10], pf10);
         }
         if (tid == 64) { atomicAdd(&g_lzprof[6], pf[6]); atomicAdd(&g_lzprof[7], pf[7]); }
         if (tid == 31 * 32) atomicAdd(&g_lzprof[0], pf31);
