@@ -78,12 +78,12 @@ void build_crc_tables(uint32_t* tab /* CRC_TAB_WORDS */)
 const LevelParams& level_params(int level)
 {
     // good/lazy/nice: the reference's configuration_table (lib/zlib/deflate.c:134-146).
-    // depth: candidates examined per position (every position is searched, chains keyed on 4 bytes).
+    // depth: candidates examined per position (every position is searched, chains keyed on 6 bytes).
     static const LevelParams t[10] = {
-        {0, 0, 0, 0, 0},
-        {1, 8, 4, 0, 1},   {2, 16, 5, 0, 1},   {4, 32, 6, 0, 1},
-        {8, 16, 4, 1, 1},  {16, 32, 16, 1, 1}, {32, 128, 16, 1, 1},
-        {40, 128, 32, 1, 1}, {64, 258, 128, 1, 1}, {96, 258, 258, 1, 1}};
+        {0, 0, 0, 0, 0, 0},
+        {1, 8, 4, 0, 1, 1},   {2, 16, 5, 0, 1, 1},   {4, 32, 6, 0, 1, 1},
+        {4, 16, 4, 1, 1, 1},  {6, 32, 16, 1, 1, 1},  {8, 128, 16, 1, 1, 1},
+        {16, 128, 32, 1, 1, 1}, {32, 258, 128, 1, 1, 1}, {64, 258, 258, 1, 1, 1}};
     return t[level];
 }
 

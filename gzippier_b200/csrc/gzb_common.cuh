@@ -21,7 +21,8 @@ constexpr int      RING        = 65536;           // bytes of window kept in sha
 constexpr int      LINK_RING   = 32768 + 2 * TILE;// chain links kept in shared memory
 constexpr int      MAXD        = 32768;           // farthest match (deflate's limit)
 constexpr int      TOO_FAR     = 4096;            // lib/zlib/deflate.c:110-112
-constexpr int      HBITS       = 14;              // buckets of the 4-byte chain table
+constexpr int      HBITS       = 14;              // buckets of the 6-byte chain table
+constexpr int      H4BITS      = 12;              // buckets of the 4-byte single-entry table
 constexpr int      H3BITS      = 12;              // buckets of the 3-byte single-entry table
 constexpr int      BLOCK_SPAN  = 65536;           // input bytes per deflate block
 constexpr int      MAX_BPC     = MAX_CHUNK / BLOCK_SPAN;   // blocks per chunk
@@ -33,7 +34,7 @@ constexpr int      HDR_BYTES   = 608;             // worst case 14 + 57 + 316*14
 // Search effort per level.  good/lazy/nice are the reference's configuration_table
 // (lib/zlib/deflate.c:134-146); depth replaces max_chain (DESIGN.md "Level semantics").
 struct LevelParams {
-    int depth, nice, max_lazy, lazy_parse, use_h3;
+    int depth, nice, max_lazy, lazy_parse, use_h3, use_h4;
 };
 
 // One deflate block.  Written by k_lz77 (histograms, token range, input range),
@@ -123,7 +124,8 @@ __host__ __device__ __forceinline__ uint32_t dist_base(uint32_t code)
     return 1u + ((2u + (code & 1u)) << e);
 }
 
-__host__ __device__ __forceinline__ uint32_t hash4(uint32_t v) { return (v * 0x9E3779B1u) >> (32 - HBITS); }
+__host__ __device__ __forceinline__ uint32_t hash6(uint32_t lo, uint32_t hi16) { return (lo * 0x9E3779B1u + hi16 * 0x85EBCA6Bu) >> (32 - HBITS); }
+__host__ __device__ __forceinline__ uint32_t hash4(uint32_t v) { return (v * 0x9E3779B1u) >> (32 - H4BITS); }
 __host__ __device__ __forceinline__ uint32_t hash3(uint32_t v) { return ((v << 8) * 0x9E3779B1u) >> (32 - H3BITS); }
 
 // CRC-32 (reflected, poly 0xEDB88320) helpers shared by k_crc32 and k_layout.

@@ -11,11 +11,11 @@
 // One persistent CTA (1024 threads, ~200 KB shared memory) per SM, chunks handed out by an
 // atomic counter.  Shared memory holds the whole search state of the chunk:
 //   ring   64 KiB  window bytes, stream position & 0xFFFF  (dictionary + chunk stream)
-//   link   72 KiB  u16 delta to the previous position in the same 4-byte bucket (0 = none),
+//   link   72 KiB  u16 delta to the previous position in the same 6-byte bucket (0 = none),
 //                  indexed by stream position mod LINK_RING; deltas need no sliding
-//   head   32 KiB  u16 last position (mod 64 Ki) per 4-byte bucket -- inserter-private
-//   head3   8 KiB  u16 last position per 3-byte bucket (single entry, no chain)
-//   c3      8 KiB  per-position delta to the most recent 3-byte twin, double-buffered per tile
+//   head   32 KiB  u16 last position (mod 64 Ki) per 6-byte bucket -- inserter-private
+//   head3/4 8+8 KiB u16 last position per 3-byte / 4-byte bucket (single entry, no chain)
+//   c3/c4  8+8 KiB per-position delta to the most recent 3-byte / 4-byte twin, double-buffered per tile
 //   mlen/mdist 12 KiB  per-position best match of the last two tiles
 // Stale/aliased head entries are detected by re-hashing the bytes at the candidate, which makes
 // the chains exactly "all earlier positions of the same bucket, most recent first"
@@ -40,7 +40,9 @@ struct Smem {
     uint16_t link[LINK_RING];
     uint16_t head[1 << HBITS];
     uint16_t head3[1 << H3BITS];
+    uint16_t head4[1 << H4BITS];
     uint16_t c3[2][TILE];
+    uint16_t c4[2][TILE];
     uint16_t mdist[MRING];                // dist-1, 0xFFFF = no match
     uint8_t  mlen[MRING];                 // len-3
     uint32_t lfreq[288];
@@ -108,36 +110,44 @@ __device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n
 }
 
 // Insert the positions of tile t into one hash table, in stream order.  One warp; 32 consecutive
-// positions per step.  CHAIN: 4-byte buckets, result = link delta per position (S.link);
-// otherwise 3-byte buckets, result = delta to the most recent twin within TOO_FAR (S.c3).
+// positions per step.  KIND 0: 6-byte buckets, result = link delta per position (S.link);
+// KIND 1 / 2: 3-byte / 4-byte buckets, result = delta to the most recent twin (S.c3 within TOO_FAR / S.c4).
 // Every lane reads the bucket head, then all lanes write their position and read it back: a lane
 // that does not find its own position shares its bucket with another lane of the same step
 // (MATCH.ANY would tell the same, at ~500 cycles per step when the 32 values are distinct);
 // only those rare groups are then ordered by lane with ballots.
-template <bool CHAIN>
+template <int KIND>
+__device__ __forceinline__ uint32_t bucket_of(uint32_t v, uint32_t v2)
+{
+    return KIND == 0 ? hash6(v, v2 & 0xFFFFu) : KIND == 1 ? hash3(v) : hash4(v);
+}
+template <int KIND>
 __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane)
 {
     const uint32_t base = t * TILE;
-    uint16_t* table = CHAIN ? S.head : S.head3;
-    uint16_t* c3 = S.c3[t & 1];
+    uint16_t* table = KIND == 0 ? S.head : KIND == 1 ? S.head3 : S.head4;
+    uint16_t* cx = KIND == 1 ? S.c3[t & 1] : S.c4[t & 1];
+    const uint32_t maxd = KIND == 1 ? (uint32_t)TOO_FAR : 32767u;
     uint32_t slot = base % LINK_RING + lane;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    uint32_t v = ring_ld32(S.ring32, base + lane);
+    uint32_t v = ring_ld32(S.ring32, base + lane), v2 = KIND == 0 ? ring_ld32(S.ring32, base + lane + 4u) : 0u;
     for (uint32_t i = 0; i < GROUPS_PER_TILE; i++, slot += 32) {
         const uint32_t p = base + i * 32u + lane;
         if (base + i * 32u >= n_s) break;                       // nothing past the end is ever searched
         if (slot >= LINK_RING) slot -= LINK_RING;
-        const uint32_t h = CHAIN ? hash4(v) : hash3(v);
+        const uint32_t h = bucket_of<KIND>(v, v2);
         const uint32_t old = table[h];
         // candidate = bucket head as of the previous step; fetch its bytes now, judge them later
         const uint32_t d = (p - old) & 0xFFFFu;
-        const bool in_range = d != 0u && d <= (CHAIN ? 32767u : (uint32_t)TOO_FAR) && d <= p;
+        const bool in_range = d != 0u && d <= maxd && d <= p;
         const uint32_t cv = ring_ld32(S.ring32, in_range ? p - d : p);
+        const uint32_t cv2 = KIND == 0 ? ring_ld32(S.ring32, (in_range ? p - d : p) + 4u) : 0u;
         __syncwarp();
         table[h] = (uint16_t)p;
         __syncwarp();
         const uint32_t won = table[h];
         v = ring_ld32(S.ring32, p + 32u);                       // next step's bytes (ring is read-only here)
+        if (KIND == 0) v2 = ring_ld32(S.ring32, p + 36u);
         uint32_t todo = __ballot_sync(FULL, won != (p & 0xFFFFu));
         int lower_lane = -1;
         while (todo) {                                          // uniform; rare
@@ -153,8 +163,8 @@ __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane)
         }
         uint32_t delta = 0;
         if (lower_lane >= 0) delta = lane - (uint32_t)lower_lane;
-        else if (in_range && (CHAIN ? hash4(cv) : hash3(cv)) == h) delta = d;     // stale/aliased heads fail the re-hash
-        if (CHAIN) S.link[slot] = (uint16_t)delta; else c3[i * 32u + lane] = (uint16_t)delta;
+        else if (in_range && bucket_of<KIND>(cv, cv2) == h) delta = d;     // stale/aliased heads fail the re-hash
+        if (KIND == 0) S.link[slot] = (uint16_t)delta; else cx[i * 32u + lane] = (uint16_t)delta;
         __syncwarp();
     }
 }
@@ -215,6 +225,13 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
         }
     }
     if (maxlen >= 3) {
+        if (best < 6 && lp.use_h4) {
+            uint32_t d4 = S.c4[t & 1][g * 32u + lane];
+            if (d4 != 0u && d4 <= limit && maxlen >= 4) {
+                int l = match_len(S.ring32, p, p - d4, maxlen);
+                if (l >= 4 && l > best) { best = l; bdist = d4; }
+            }
+        }
         if (best < 3 && lp.use_h3) {
             uint32_t d3 = S.c3[t & 1][g * 32u + lane];
             if (d3 != 0u && d3 <= min(limit, (uint32_t)TOO_FAR)) {
@@ -288,6 +305,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         // ---- per-chunk reset ----
         for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = 0;
         for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = 0;
+        for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = 0;
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
         if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[0] = 0; S.grp_ctr[1] = 0; }
@@ -302,11 +320,13 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             if (tid == 0) S.grp_ctr[(k + 1) & 1] = 0;           // last used two barriers ago
             // the SMSP arbiter favours the highest warp ids: give them the two serial inserter roles
             if (warp == 31) {
-                if (k + 1 < (int)ntiles) insert_tile<true>(S, (uint32_t)(k + 1), n_s, lane);
+                if (k + 1 < (int)ntiles) insert_tile<0>(S, (uint32_t)(k + 1), n_s, lane);
                 if (lane == 0) pf31 += (unsigned long long)(clock64() - t0);
             } else if (warp == 30) {
-                if (k + 1 < (int)ntiles) insert_tile<false>(S, (uint32_t)(k + 1), n_s, lane);
+                if (k + 1 < (int)ntiles) insert_tile<1>(S, (uint32_t)(k + 1), n_s, lane);
                 load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
+            } else if (warp == 29) {
+                if (k + 1 < (int)ntiles) insert_tile<2>(S, (uint32_t)(k + 1), n_s, lane);
             }
             const bool ctile = k >= (int)first_ctile;
             if (ctile) {

@@ -10,9 +10,11 @@
  * The engine's semantics are defined so that they do NOT depend on how the
  * GPU schedules work:
  *   match(p)   = best (len, dist) over the first `depth` earlier positions, most
- *                recent first, that share p's hash bucket and lie within
+ *                recent first, that share p's 6-BYTE hash bucket and lie within
  *                `maxd`; a candidate replaces the best only if strictly longer;
- *                the walk stops at len >= nice.           [cf. longest_match,
+ *                the walk stops at len >= nice.  If that gives less than 6, the
+ *                most recent 4-byte twin is tried, and if still nothing, the
+ *                most recent 3-byte twin within TOO_FAR.   [cf. longest_match,
  *                lib/zlib/deflate.c:1236-1377]
  *   next(p)    = p+1 (literal) or p+len (match), a pure function of match(p),
  *                match(p+1): greedy for levels 1-3 [deflate_fast :1824-1918],
@@ -47,48 +49,53 @@ int gzm_dist_code(int dist) /* 1..32768 -> 0..29 */
 /* ---------------- level table ---------------- */
 /* good/lazy/nice are the reference's configuration_table (lib/zlib/deflate.c:134-146);
  * depth is the engine's own candidate budget per position (every position is searched
- * and the chains are keyed on 4 bytes, so far fewer probes are needed than zlib's max_chain
+ * and the chains are keyed on 6 bytes, so far fewer probes are needed than zlib's max_chain
  * for the same ratio -- see DESIGN.md "Level semantics"). */
 void gzm_level_params(int level, gzm_params *p)
 {
     static const struct { int good, lazy, nice, chain, depth; } t[10] = {
         {0, 0, 0, 0, 0},
         {4, 4, 8, 4, 1}, {4, 5, 16, 8, 2}, {4, 6, 32, 32, 4},
-        {4, 4, 16, 16, 8}, {8, 16, 32, 32, 16}, {8, 16, 128, 128, 32},
-        {8, 32, 128, 256, 40}, {32, 128, 258, 1024, 64}, {32, 258, 258, 4096, 96}};
+        {4, 4, 16, 16, 4}, {8, 16, 32, 32, 6}, {8, 16, 128, 128, 8},
+        {8, 32, 128, 256, 16}, {32, 128, 258, 1024, 32}, {32, 258, 258, 4096, 64}};
     memset(p, 0, sizeof(*p));
     p->level = level;
     p->good = t[level].good; p->max_lazy = t[level].lazy; p->nice = t[level].nice;
     p->ref_chain = t[level].chain; p->depth = t[level].depth;
     p->lazy_parse = level >= 4;
     p->maxd = GZM_MAXD; p->hbits = GZM_HBITS; p->block_span = GZM_BLOCK_SPAN;
-    p->chunk = 131072; p->dict = 32768; p->use_h3 = 1;
+    p->chunk = 131072; p->dict = 32768; p->use_h3 = 1; p->use_h4 = 1;
 }
 
 /* ---------------- match finder ---------------- */
 static inline uint32_t ld32(const uint8_t *p) { uint32_t v; memcpy(&v, p, 4); return v; }
-uint32_t gzm_hash4(uint32_t v, int hbits) { return (v * 0x9E3779B1u) >> (32 - hbits); }
+uint32_t gzm_hash6(uint32_t lo, uint32_t hi16, int hbits) { return (lo * 0x9E3779B1u + hi16 * 0x85EBCA6Bu) >> (32 - hbits); }
+uint32_t gzm_hash4(uint32_t v) { return (v * 0x9E3779B1u) >> (32 - GZM_H4BITS); }
 uint32_t gzm_hash3(uint32_t v) { return ((v << 8) * 0x9E3779B1u) >> (32 - GZM_H3BITS); }
 
+static int common_len(const uint8_t *a, const uint8_t *b, int maxlen) { int l = 0; while (l < maxlen && a[l] == b[l]) l++; return l; }
+
 /* stream = dict||chunk, D = dict length, n = total stream length.  Positions < D are inserted only.
- * bytes beyond the stream end read as zero for hashing (positions n-3..n-1). */
+ * bytes beyond the stream end read as zero for hashing (positions n-5..n-1). */
 void gzm_find_matches(const gzm_params *P, const uint8_t *s, int D, int n, uint16_t *mlen, uint16_t *mdist)
 {
-    int hsize = 1 << P->hbits, h3size = 1 << GZM_H3BITS;
+    int hsize = 1 << P->hbits, h3size = 1 << GZM_H3BITS, h4size = 1 << GZM_H4BITS;
     int32_t *head = (int32_t *)malloc(sizeof(int32_t) * hsize);
     int32_t *head3 = (int32_t *)malloc(sizeof(int32_t) * h3size);
+    int32_t *head4 = (int32_t *)malloc(sizeof(int32_t) * h4size);
     int32_t *link = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n + 1));
     for (int i = 0; i < hsize; i++) head[i] = -1;
     for (int i = 0; i < h3size; i++) head3[i] = -1;
+    for (int i = 0; i < h4size; i++) head4[i] = -1;
     for (int p = 0; p < n; p++) {
-        uint8_t tmp[4] = {0, 0, 0, 0};
-        for (int k = 0; k < 4 && p + k < n; k++) tmp[k] = s[p + k];
-        uint32_t h = gzm_hash4(P->hash3 ? (ld32(tmp) & 0xffffffu) : ld32(tmp), P->hbits);
-        uint32_t h3 = gzm_hash3(ld32(tmp));
-        int32_t prev = head[h], prev3 = head3[h3];
+        uint8_t tmp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int k = 0; k < 6 && p + k < n; k++) tmp[k] = s[p + k];
+        uint32_t lo = ld32(tmp), hi16 = (uint32_t)tmp[4] | ((uint32_t)tmp[5] << 8);
+        uint32_t h = gzm_hash6(lo, hi16, P->hbits), h4 = gzm_hash4(lo), h3 = gzm_hash3(lo);
+        int32_t prev = head[h], prev4 = head4[h4], prev3 = head3[h3];
         /* the GPU stores 16-bit deltas: a gap above 32767 ends the chain */
         link[p] = (prev >= 0 && p - prev <= 32767) ? prev : -1;
-        head[h] = p; head3[h3] = p;
+        head[h] = p; head4[h4] = p; head3[h3] = p;
         if (p < D) continue;
         int maxlen = n - p < 258 ? n - p : 258;
         int best = 2, bdist = 0;
@@ -97,23 +104,26 @@ void gzm_find_matches(const gzm_params *P, const uint8_t *s, int D, int n, uint1
         int c = link[p], depth = P->depth;
         while (c >= 0 && p - c <= limit && depth-- > 0) {
             if (maxlen > best && s[c + best] == s[p + best]) {
-                int l = 0;
-                while (l < maxlen && s[c + l] == s[p + l]) l++;
+                int l = common_len(s + c, s + p, maxlen);
                 if (l > best) { best = l; bdist = p - c; if (l >= nice) break; }
             }
             c = link[c];
         }
-        /* no match of 4+ on the chain: try the most recent 3-byte twin (single-entry table) */
+        /* nothing of 6+ on the chain: try the most recent 4-byte twin (single-entry table) */
+        if (best < 6 && P->use_h4 && prev4 >= 0 && p - prev4 <= (limit < 32767 ? limit : 32767) && maxlen >= 4) {
+            int l = common_len(s + prev4, s + p, maxlen);
+            if (l >= 4 && l > best) { best = l; bdist = p - prev4; }
+        }
+        /* still nothing: the most recent 3-byte twin */
         if (best < 3 && P->use_h3 && prev3 >= 0 && p - prev3 <= (limit < GZM_TOO_FAR ? limit : GZM_TOO_FAR) && maxlen >= 3) {
-            int l = 0;
-            while (l < maxlen && s[prev3 + l] == s[p + l]) l++;
+            int l = common_len(s + prev3, s + p, maxlen);
             if (l >= 3) { best = l; bdist = p - prev3; }
         }
         if (best == 3 && bdist > GZM_TOO_FAR) best = 2;       /* TOO_FAR, deflate.c:110-112,1972-1981 */
         if (best < 3) { mlen[p - D] = 0; mdist[p - D] = 0; }
         else { mlen[p - D] = (uint16_t)best; mdist[p - D] = (uint16_t)bdist; }
     }
-    free(head); free(head3); free(link);
+    free(head); free(head3); free(head4); free(link);
 }
 
 /* ---------------- parse ---------------- */

@@ -9,6 +9,7 @@ extern "C" {
 
 #define GZM_HBITS       14
 #define GZM_H3BITS      12                        /* single-entry table of most recent 3-byte twins */
+#define GZM_H4BITS      12                        /* single-entry table of most recent 4-byte twins */
 #define GZM_TILE        2048                      /* positions per pipeline step of the LZ77 kernel */
 #define GZM_MAXD        32768                     /* farthest match (the link ring is 32768+2*TILE) */
 #define GZM_TOO_FAR     4096                      /* lib/zlib/deflate.c:110-112                      */
@@ -19,8 +20,8 @@ typedef struct gzm_params {
     int depth;                                    /* candidates examined per position                */
     int lazy_parse;                               /* 0: greedy (levels 1-3), 1: lazy (4-9)           */
     int maxd, hbits, block_span, chunk, dict;
-    int use_h3;
-    int hash3;                                    /* experiment: key chains on 3 bytes */
+    int use_h3;                                   /* fall back to the most recent 3-byte twin when nothing longer exists */
+    int use_h4;                                   /* ... and to the most recent 4-byte twin when the chain gives < 6  */
 } gzm_params;
 
 typedef struct gzm_block_plan {
@@ -35,7 +36,8 @@ typedef struct gzm_block_plan {
 typedef struct gzm_chunk_stats { uint64_t tokens, matches, blocks[3]; } gzm_chunk_stats;
 
 void     gzm_level_params(int level, gzm_params *p);
-uint32_t gzm_hash4(uint32_t v, int hbits);
+uint32_t gzm_hash6(uint32_t lo, uint32_t hi16, int hbits);
+uint32_t gzm_hash4(uint32_t v);
 uint32_t gzm_hash3(uint32_t v);
 int      gzm_len_code(int len);
 int      gzm_dist_code(int dist);
