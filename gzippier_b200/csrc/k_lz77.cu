@@ -31,6 +31,7 @@ __device__ unsigned long long g_lzprof[16];
 namespace {
 
 constexpr uint32_t FULL = 0xFFFFFFFFu;
+constexpr uint32_t NOPOS = 0xFFFFFFFFu;
 constexpr int GROUPS_PER_TILE = TILE / 32;
 constexpr int RING_MIRROR = 272;         // >= 258 + 3 (longest compare) + 4, multiple of 16
 constexpr int MRING = 2 * TILE;           // per-position match results kept for two tiles
@@ -50,7 +51,7 @@ struct Smem {
     uint32_t masks[TILE / 32];            // token-start bitmap of the tile being parsed
     uint32_t seg_prefix[TILE / 32 + 1];
     uint16_t jump[2][TILE];               // pointer doubling: 2^r-th successor of every position (TILE = leaves the tile)
-    uint32_t grp_ctr[2];                  // dynamic group scheduler, alternating per pipeline step
+    uint32_t grp_ctr[2];                  // dynamic group scheduler of the search phase
     uint32_t chunk_idx;
     uint32_t entry;                       // next token start (stream position)
     uint32_t ntok;                        // tokens emitted so far in this chunk
@@ -58,6 +59,8 @@ struct Smem {
     uint32_t blk_tok0;                    // token index where the current block began
     uint32_t blk_in0;                     // chunk-relative input offset where it began
     uint32_t extra_lit;                   // 1 if the final position needs its own literal
+    uint32_t carry_pos, carry_len, carry_dist;   // match of the last position of the tile before the one being parsed
+                                          // (its slot in mlen/mdist is rewritten by the concurrent search)
 };
 
 __device__ __forceinline__ uint32_t ring_ld32(const uint32_t* ring32, uint32_t pos)
@@ -109,63 +112,101 @@ __device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n
     }
 }
 
-// Insert the positions of tile t into one hash table, in stream order.  One warp; 32 consecutive
-// positions per step.  KIND 0: 6-byte buckets, result = link delta per position (S.link);
-// KIND 1 / 2: 3-byte / 4-byte buckets, result = delta to the most recent twin (S.c3 within TOO_FAR / S.c4).
-// Every lane reads the bucket head, then all lanes write their position and read it back: a lane
-// that does not find its own position shares its bucket with another lane of the same step
-// (MATCH.ANY would tell the same, at ~500 cycles per step when the 32 values are distinct);
-// only those rare groups are then ordered by lane with ballots.
+// ---- insertion ---------------------------------------------------------------------------------------
+// Inserting a tile into a hash table is serial per bucket, and one warp doing 64 steps of 32 positions is
+// latency-bound -- all the more so next to 29 busy search warps, since a warp issues in order and every
+// instruction of the step waits for its turn.  So the step is stripped to what IS serial:
+//   hash_tile    (all threads, before)  bucket of every position of the tile, for the three tables
+//   insert_tile  (one warp per table)   old = head[h]; head[h] = p; store `old` raw.  Lanes of a step that share
+//                                       a bucket are detected by write-then-read-back and ordered with ballots
+//                                       (MATCH.ANY would tell the same, at ~500 cycles per step)
+//   finish_tile  (all threads, after)   raw head -> delta, rejecting stale/aliased heads by re-hashing the bytes
+//                                       at the candidate, so a chain is exactly "all earlier positions of the
+//                                       bucket, most recent first"
+// KIND 0: 6-byte buckets -> S.link (chains); KIND 1 / 2: 3-byte / 4-byte buckets -> S.c3 (within TOO_FAR) / S.c4.
 template <int KIND>
 __device__ __forceinline__ uint32_t bucket_of(uint32_t v, uint32_t v2)
 {
     return KIND == 0 ? hash6(v, v2 & 0xFFFFu) : KIND == 1 ? hash3(v) : hash4(v);
 }
+
+__device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
+{
+    // the bucket of a position is parked where its link / c3 / c4 entry will go: those slots are dead until insertion
+#pragma unroll
+    for (int j = 0; j < TILE / LZ_THREADS; j++) {
+        const uint32_t o = tid + (uint32_t)j * LZ_THREADS, p = t * TILE + o;
+        const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);      // zero past the end of the stream
+        uint32_t slot = (t * TILE) % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
+        S.link[slot] = (uint16_t)bucket_of<0>(v, v2); S.c3[t & 1][o] = (uint16_t)bucket_of<1>(v, v2); S.c4[t & 1][o] = (uint16_t)bucket_of<2>(v, v2);
+    }
+}
+
+// cls / cmask: only the buckets with (bucket & cmask) == cls are inserted (0, 0 = all).
 template <int KIND>
-__device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane)
+__device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, uint32_t cls, uint32_t cmask)
 {
     const uint32_t base = t * TILE;
     uint16_t* table = KIND == 0 ? S.head : KIND == 1 ? S.head3 : S.head4;
     uint16_t* cx = KIND == 1 ? S.c3[t & 1] : S.c4[t & 1];
-    const uint32_t maxd = KIND == 1 ? (uint32_t)TOO_FAR : 32767u;
     uint32_t slot = base % LINK_RING + lane;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    uint32_t v = ring_ld32(S.ring32, base + lane), v2 = KIND == 0 ? ring_ld32(S.ring32, base + lane + 4u) : 0u;
-    for (uint32_t i = 0; i < GROUPS_PER_TILE; i++, slot += 32) {
-        const uint32_t p = base + i * 32u + lane;
+    uint32_t hn = KIND == 0 ? (uint32_t)S.link[slot] : (uint32_t)cx[lane];
+    for (uint32_t i = 0; i < GROUPS_PER_TILE; i++) {
         if (base + i * 32u >= n_s) break;                       // nothing past the end is ever searched
-        if (slot >= LINK_RING) slot -= LINK_RING;
-        const uint32_t h = bucket_of<KIND>(v, v2);
-        const uint32_t old = table[h];
-        // candidate = bucket head as of the previous step; fetch its bytes now, judge them later
-        const uint32_t d = (p - old) & 0xFFFFu;
-        const bool in_range = d != 0u && d <= maxd && d <= p;
-        const uint32_t cv = ring_ld32(S.ring32, in_range ? p - d : p);
-        const uint32_t cv2 = KIND == 0 ? ring_ld32(S.ring32, (in_range ? p - d : p) + 4u) : 0u;
+        const uint32_t p16 = (base + i * 32u + lane) & 0xFFFFu;
+        uint32_t h = hn;
+        const uint32_t slot_now = slot;
+        slot += 32u; if (slot >= LINK_RING) slot -= LINK_RING;
+        if (i + 1u < GROUPS_PER_TILE) hn = KIND == 0 ? (uint32_t)S.link[slot] : (uint32_t)cx[(i + 1u) * 32u + lane];   // next step's buckets
+        const bool act = (h & cmask) == cls;
+        if (!act) h = 0xFFFFFFFFu;                              // never equal to a real bucket
+        uint32_t raw = act ? (uint32_t)table[h] : 0u;
         __syncwarp();
-        table[h] = (uint16_t)p;
+        if (act) table[h] = (uint16_t)p16;
         __syncwarp();
-        const uint32_t won = table[h];
-        v = ring_ld32(S.ring32, p + 32u);                       // next step's bytes (ring is read-only here)
-        if (KIND == 0) v2 = ring_ld32(S.ring32, p + 36u);
-        uint32_t todo = __ballot_sync(FULL, won != (p & 0xFFFFu));
-        int lower_lane = -1;
+        uint32_t todo = __ballot_sync(FULL, act && (uint32_t)table[h] != p16);
         while (todo) {                                          // uniform; rare
             const int leader = __ffs(todo) - 1;
             const uint32_t hv = __shfl_sync(FULL, h, leader);
             const uint32_t grp = __ballot_sync(FULL, h == hv);
             if (h == hv) {
                 const uint32_t lower = grp & lt_mask;
-                if (lower) lower_lane = 31 - __clz(lower);
-                if ((grp >> lane) == 1u) table[h] = (uint16_t)p;    // the last position of the step owns the bucket
+                if (lower) raw = (p16 - (lane - (uint32_t)(31 - __clz(lower)))) & 0xFFFFu;   // the nearest lower lane of the bucket
+                if ((grp >> lane) == 1u) table[h] = (uint16_t)p16;  // the last position of the step owns the bucket
             }
             todo &= ~grp;
         }
-        uint32_t delta = 0;
-        if (lower_lane >= 0) delta = lane - (uint32_t)lower_lane;
-        else if (in_range && bucket_of<KIND>(cv, cv2) == h) delta = d;     // stale/aliased heads fail the re-hash
-        if (KIND == 0) S.link[slot] = (uint16_t)delta; else cx[i * 32u + lane] = (uint16_t)delta;
+        if (act) { if (KIND == 0) S.link[slot_now] = (uint16_t)raw; else cx[i * 32u + lane] = (uint16_t)raw; }
         __syncwarp();
+    }
+}
+
+__device__ void finish_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t tid)
+{
+    const uint32_t base = t * TILE;
+#pragma unroll
+    for (int j = 0; j < TILE / LZ_THREADS; j++) {
+        const uint32_t o = tid + (uint32_t)j * LZ_THREADS, p = base + o;
+        if (p >= n_s) continue;
+        const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);
+        uint32_t slot = base % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
+        {
+            const uint32_t d = (p - (uint32_t)S.link[slot]) & 0xFFFFu;
+            const bool ok = d != 0u && d <= 32767u && d <= p;
+            const uint32_t c = ok ? p - d : p;
+            S.link[slot] = (uint16_t)((ok && bucket_of<0>(ring_ld32(S.ring32, c), ring_ld32(S.ring32, c + 4u)) == bucket_of<0>(v, v2)) ? d : 0u);
+        }
+        {
+            const uint32_t d = (p - (uint32_t)S.c3[t & 1][o]) & 0xFFFFu;
+            const bool ok = d != 0u && d <= (uint32_t)TOO_FAR && d <= p;
+            S.c3[t & 1][o] = (uint16_t)((ok && hash3(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash3(v)) ? d : 0u);
+        }
+        {
+            const uint32_t d = (p - (uint32_t)S.c4[t & 1][o]) & 0xFFFFu;
+            const bool ok = d != 0u && d <= 32767u && d <= p;
+            S.c4[t & 1][o] = (uint16_t)((ok && hash4(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash4(v)) ? d : 0u);
+        }
     }
 }
 
@@ -247,28 +288,150 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
 }
 
 // next(p): the parse rule (engine_model.c gzm_parse).  Returns the step from p and whether p is a literal.
-__device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams& lp, uint32_t p, uint32_t n_s, bool& lit)
+__device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams& lp, uint32_t p, uint32_t n_s, bool& lit, uint32_t& dist)
 {
-    uint32_t mi = p & (MRING - 1);
-    uint32_t md = S.mdist[mi];
-    uint32_t L = (uint32_t)S.mlen[mi] + 3u;
+    uint32_t md, L;
+    if (p == S.carry_pos) { md = S.carry_dist; L = S.carry_len + 3u; }
+    else { const uint32_t mi = p & (MRING - 1); md = S.mdist[mi]; L = (uint32_t)S.mlen[mi] + 3u; }
     lit = (md == 0xFFFFu);
+    dist = md + 1u;
     if (!lit && lp.lazy_parse && L < (uint32_t)lp.max_lazy && p + 1u < n_s) {
-        uint32_t mj = (p + 1u) & (MRING - 1);
+        const uint32_t mj = (p + 1u) & (MRING - 1);
         if (S.mdist[mj] != 0xFFFFu && (uint32_t)S.mlen[mj] + 3u > L) lit = true;
     }
     return lit ? 1u : L;
 }
 
-__device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid)
+// ---- parse + emission of one tile, by the parser group (warps 0..PARSE_WARPS-1, named barrier 1) -------
+constexpr int PARSE_WARPS = 8;
+constexpr int PARSE_WARP0 = 18;              // warps 18..25
+constexpr int PG = PARSE_WARPS * 32;              // threads of the parser group
+constexpr int PPT = (TILE + PG - 1) / PG;         // positions per parser thread
+
+__device__ __forceinline__ void group_sync() { asm volatile("bar.sync 1, %0;" :: "n"(PG) : "memory"); }
+__device__ __forceinline__ bool group_sync_or(bool pred)
+{
+    uint32_t out;
+    asm volatile("{ .reg .pred p, q; setp.ne.u32 p, %1, 0; bar.red.or.pred q, 1, %2, p; selp.u32 %0, 1, 0, q; }"
+                 : "=r"(out) : "r"((uint32_t)pred), "n"(PG) : "memory");
+    return out != 0u;
+}
+
+__device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid, uint32_t nthr)
 {
     // histograms of the block that just ended -> global; reset for the next one
-    for (uint32_t i = tid; i < 288u; i += LZ_THREADS) { brec->lfreq[i] = S.lfreq[i]; S.lfreq[i] = 0; }
+    for (uint32_t i = tid; i < 288u; i += nthr) { brec->lfreq[i] = S.lfreq[i]; S.lfreq[i] = 0; }
     if (tid < 32u) { brec->dfreq[tid] = S.dfreq[tid]; S.dfreq[tid] = 0; }
     if (tid == 0) {
         brec->tok_begin = S.blk_tok0; brec->tok_count = S.ntok - S.blk_tok0;
         brec->in_off = S.blk_in0; brec->in_bytes = in_end - S.blk_in0;
     }
+}
+
+// Token starts of tile k = the positions reachable from the entry point along next(), a pure function of the
+// per-position matches: pointer doubling over all positions of the tile (round r marks what is 2^r hops behind
+// a marked position).  Then every marked position emits its token; index = prefix popcount of the marks.
+__device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t D, uint32_t n_s, uint32_t ntiles, uint32_t nblocks,
+                                uint32_t* __restrict__ tok, BlockRec* __restrict__ brecs, uint32_t gtid)
+{
+    const uint32_t lane = gtid & 31u, warp = gtid >> 5;
+    const bool last = (k == (int)ntiles - 1);
+    const int base = k * TILE - 1;                        // decidable positions: [base, hi) (lazy needs mlen[p+1])
+    const int hi = last ? (int)n_s : base + TILE;
+    const int hi_w = min(hi, base + TILE);
+    // block boundary: tokens emitted from this tile on belong to the next block
+    const uint32_t q0 = (uint32_t)k * TILE - D;           // chunk-relative start of the tile
+    if (q0 != 0u && (q0 % BLOCK_SPAN) == 0u && S.blk + 1u < nblocks) {
+        flush_block(S, &brecs[S.blk], S.entry - D, gtid, PG);
+        group_sync();
+        if (gtid == 0) { S.blk++; S.blk_tok0 = S.ntok; S.blk_in0 = S.entry - D; }
+        group_sync();
+    }
+    const int entry = (int)S.entry;                       // >= base by construction
+    const int lim = hi_w - base;                          // positions [0, lim) of the tile can start a token
+    int rawnx[PPT];
+#pragma unroll
+    for (int r = 0; r < PPT; r++) {
+        const int o = (int)gtid + r * PG;
+        int nx = TILE;
+        if (o < lim) { bool lit; uint32_t dd; nx = o + (int)parse_step(S, lp, (uint32_t)(base + o), n_s, lit, dd); }
+        rawnx[r] = nx;
+        if (o < TILE) S.jump[0][o] = (uint16_t)(nx < lim ? nx : TILE);
+    }
+    if (gtid < TILE / 32) S.masks[gtid] = (entry - base < lim && (uint32_t)(entry - base) / 32u == gtid) ? 1u << ((entry - base) & 31) : 0u;
+    group_sync();
+    for (int rd = 0;; rd++) {
+        const uint16_t* jc = S.jump[rd & 1]; uint16_t* jn = S.jump[(rd + 1) & 1];
+        bool more = false;
+#pragma unroll
+        for (int r = 0; r < PPT; r++) {
+            const int o = (int)gtid + r * PG;
+            if (o < TILE) {
+                const uint32_t j = jc[o];
+                uint32_t jj = TILE;
+                if (j < (uint32_t)TILE) {
+                    if ((S.masks[o >> 5] >> (o & 31)) & 1u) { atomicOr(&S.masks[j >> 5], 1u << (j & 31u)); more = true; }
+                    jj = jc[j];
+                }
+                jn[o] = (uint16_t)jj;
+            }
+        }
+        if (!group_sync_or(more)) break;
+    }
+    // the marked position whose successor leaves the tile carries the entry point of the next tile
+    {
+        int e = -1;
+#pragma unroll
+        for (int r = 0; r < PPT; r++) {
+            const int o = (int)gtid + r * PG;
+            if (o < lim && rawnx[r] >= lim && ((S.masks[o >> 5] >> (o & 31)) & 1u)) e = base + rawnx[r];
+        }
+        if (entry - base >= lim && gtid == 0) e = entry;  // the whole tile lies inside one match
+        if (e >= 0) {
+            uint32_t extra = 0;
+            if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
+            S.entry = (uint32_t)e; S.extra_lit = extra;
+        }
+    }
+    if (warp == 0) {
+        const uint32_t c0 = (uint32_t)__popc(S.masks[2 * lane]), c1 = (uint32_t)__popc(S.masks[2 * lane + 1]);
+        uint32_t incl = c0 + c1;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= (uint32_t)o) incl += v; }
+        S.seg_prefix[2 * lane] = incl - c0 - c1;
+        S.seg_prefix[2 * lane + 1] = incl - c1;
+        if (lane == 31) S.seg_prefix[TILE / 32] = incl;
+    }
+    group_sync();
+    {
+        const uint32_t ntok0 = S.ntok;
+#pragma unroll
+        for (int r = 0; r < PPT; r++) {
+            const uint32_t o = gtid + (uint32_t)r * PG;
+            if (o >= (uint32_t)TILE) continue;
+            const uint32_t seg = o >> 5, bit = o & 31u;
+            const uint32_t mk = S.masks[seg];
+            if ((mk >> bit) & 1u) {
+                const uint32_t idx = ntok0 + S.seg_prefix[seg] + (uint32_t)__popc(mk & ((1u << bit) - 1u));
+                const uint32_t p = (uint32_t)(base + (int)o);
+                bool lit; uint32_t dist; const uint32_t step = parse_step(S, lp, p, n_s, lit, dist);
+                uint32_t tv;
+                if (lit) { tv = ring_ld8(S.ring32, p); atomicAdd(&S.lfreq[tv], 1u); }
+                else {
+                    tv = tok_match(step, dist);
+                    atomicAdd(&S.lfreq[257u + len_code(step)], 1u);
+                    atomicAdd(&S.dfreq[dist_code(dist)], 1u);
+                }
+                tok[idx] = tv;
+            }
+        }
+        if (gtid == 0 && S.extra_lit) {
+            const uint32_t tv = ring_ld8(S.ring32, (uint32_t)(base + TILE));
+            atomicAdd(&S.lfreq[tv], 1u);
+            tok[ntok0 + S.seg_prefix[TILE / 32]] = tv;
+        }
+    }
+    group_sync();
+    if (gtid == 0) { S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0; }
 }
 
 __global__ void __launch_bounds__(LZ_THREADS, 1)
@@ -299,7 +462,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         uint32_t* tok = tokens + (size_t)c * chunk;
         BlockRec* brecs = blocks + (size_t)c * bpc;
 
-        unsigned long long pf[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pf31 = 0, pf10 = 0;
+        unsigned long long pf[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         long long t0 = clock64(), t1;
 #define PF(i) do { t1 = clock64(); pf[i] += (unsigned long long)(t1 - t0); t0 = t1; } while (0)
         // ---- per-chunk reset ----
@@ -308,161 +471,69 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = 0;
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
-        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[0] = 0; S.grp_ctr[1] = 0; }
+        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[0] = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
         for (uint32_t t = 0; t < 3; t++) load_tile(S, sp, n_s, t, tid, LZ_THREADS);
         __syncthreads();
-        PF(8);
+        hash_tile(S, 0u, tid);
+        __syncthreads();
+        PF(0);
 
-        // ---- pipeline: iteration k inserts tile k+1 while tile k is searched, then parses tile k ----
-        for (int k = -1; k < (int)ntiles; k++) {
-            // stage A
-            uint32_t* gctr = &S.grp_ctr[k & 1];
-            if (tid == 0) S.grp_ctr[(k + 1) & 1] = 0;           // last used two barriers ago
-            // the SMSP arbiter favours the highest warp ids: give them the two serial inserter roles
-            if (warp == 31) {
-                if (k + 1 < (int)ntiles) insert_tile<0>(S, (uint32_t)(k + 1), n_s, lane);
-                if (lane == 0) pf31 += (unsigned long long)(clock64() - t0);
-            } else if (warp == 30) {
-                if (k + 1 < (int)ntiles) insert_tile<1>(S, (uint32_t)(k + 1), n_s, lane);
-                load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
-            } else if (warp == 29) {
-                if (k + 1 < (int)ntiles) insert_tile<2>(S, (uint32_t)(k + 1), n_s, lane);
-            }
-            const bool ctile = k >= (int)first_ctile;
-            if (ctile) {
+        // ---- pipeline: iteration k inserts tile k+1, searches tile k and parses + emits tile k-1, all at once ----
+        for (int k = -1; k <= (int)ntiles; k++) {
+            const bool do_insert = k + 1 < (int)ntiles;
+            const bool do_parse = k - 1 >= (int)first_ctile;                      // k - 1 < ntiles by the loop bound
+            const bool do_search = k >= (int)first_ctile && k < (int)ntiles;
+            // roles: three serial inserter warps (raw heads), one loader, eight parser warps; everybody else -- and
+            // everybody who is done -- searches
+            if (do_insert && warp >= 29) {
+                long long c0 = clock64();
+                const uint32_t t = (uint32_t)(k + 1);
+                if (warp == 31) insert_tile<0>(S, t, n_s, lane, 0u, 0u);
+                else if (warp == 30) insert_tile<1>(S, t, n_s, lane, 0u, 0u);
+                else insert_tile<2>(S, t, n_s, lane, 0u, 0u);
+                pf[6] += (unsigned long long)(clock64() - c0);
+            } else if (warp == 26) load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
+            else if (do_parse && warp >= (uint32_t)PARSE_WARP0 && warp < (uint32_t)(PARSE_WARP0 + PARSE_WARPS))
+                parse_emit_tile(S, lp, k - 1, D, n_s, ntiles, nblocks, tok, brecs, tid - PARSE_WARP0 * 32u);
+            PF(1);
+            if (do_search) {
                 for (;;) {
                     uint32_t g = 0;
-                    if (lane == 0) g = atomicAdd(gctr, 1u);
+                    if (lane == 0) g = atomicAdd(&S.grp_ctr[0], 1u);
                     g = __shfl_sync(FULL, g, 0);
                     if (g >= (uint32_t)GROUPS_PER_TILE) break;
                     if ((uint32_t)k * TILE + g * 32u >= n_s) continue;
                     search_group(S, lp, (uint32_t)k, g, n_s, lane);
                 }
             }
-            PF(warp == 0 ? 2 : 6);   // warp 2 (thread 64) is a pure searcher
+            PF(2);
             __syncthreads();
-            PF(warp == 0 ? 3 : 7);
-            pf[9]++;
-            if (!ctile) continue;                       // uniform: dictionary tiles are insert-only
-
-            // stage B: parse tile k.  Decidable positions: [k*TILE-1, hi) (lazy needs mlen[p+1]).
-            const bool last = (k == (int)ntiles - 1);
-            const int base = k * TILE - 1;                        // -1 for the very first tile of a stream
-            const int hi = last ? (int)n_s : base + TILE;
-            const int hi_w = min(hi, base + TILE);                // what the 32 x 64 segments cover
-            // block boundary: tokens emitted from this tile on belong to the next block
-            const uint32_t q0 = (uint32_t)k * TILE - D;           // chunk-relative start of the tile
-            if (q0 != 0u && (q0 % BLOCK_SPAN) == 0u && S.blk + 1u < nblocks) {
-                flush_block(S, &brecs[S.blk], S.entry - D, tid);
-                __syncthreads();
-                if (tid == 0) { S.blk++; S.blk_tok0 = S.ntok; S.blk_in0 = S.entry - D; }
-                __syncthreads();
+            // all threads: the links of tile k+1 become final; 6-byte buckets of tile k+2; stash the match the next
+            // parse needs from the slots the next search rewrites
+            if (do_insert) finish_tile(S, (uint32_t)(k + 1), n_s, tid);
+            if (k + 2 < (int)ntiles) hash_tile(S, (uint32_t)(k + 2), tid);
+            if (tid == 0) {
+                S.grp_ctr[0] = 0;
+                if (k >= 0) { const uint32_t cp = (uint32_t)k * TILE - 1u; S.carry_pos = cp; S.carry_len = S.mlen[cp & (MRING - 1)]; S.carry_dist = S.mdist[cp & (MRING - 1)]; }
             }
-            // parse(p) is a pure function of the per-position matches, so the token starts of the tile are the
-            // positions reachable from the entry point along next(): pointer doubling over all positions
-            // (round r marks what is 2^r hops behind a marked position) instead of a serial walk.
-            const int entry = (int)S.entry;                       // >= base by construction
-            const int lim = hi_w - base;                          // positions [0, lim) of the tile can start a token
-            int rawnx[TILE / LZ_THREADS];
-#pragma unroll
-            for (int r = 0; r < TILE / LZ_THREADS; r++) {
-                const int o = (int)tid + r * LZ_THREADS;
-                int nx = TILE;
-                if (o < lim) { bool lit; nx = o + (int)parse_step(S, lp, (uint32_t)(base + o), n_s, lit); }
-                rawnx[r] = nx;
-                S.jump[0][o] = (uint16_t)(nx < lim ? nx : TILE);
-            }
-            if (tid < TILE / 32) S.masks[tid] = (entry - base < lim && (uint32_t)(entry - base) / 32u == tid) ? 1u << ((entry - base) & 31) : 0u;
+            PF(3);
             __syncthreads();
-            PF(1);
-            for (int rd = 0;; rd++) {
-                pf10++;
-                const uint16_t* jc = S.jump[rd & 1]; uint16_t* jn = S.jump[(rd + 1) & 1];
-                bool more = false;
-#pragma unroll
-                for (int r = 0; r < TILE / LZ_THREADS; r++) {
-                    const int o = (int)tid + r * LZ_THREADS;
-                    const uint32_t j = jc[o];
-                    uint32_t jj = TILE;
-                    if (j < (uint32_t)TILE) {
-                        if ((S.masks[o >> 5] >> (o & 31)) & 1u) { atomicOr(&S.masks[j >> 5], 1u << (j & 31u)); more = true; }
-                        jj = jc[j];
-                    }
-                    jn[o] = (uint16_t)jj;
-                }
-                if (!__syncthreads_or(more)) break;
-            }
-            // the marked position whose successor leaves the tile carries the entry point of the next tile
-            {
-                int e = -1;
-#pragma unroll
-                for (int r = 0; r < TILE / LZ_THREADS; r++) {
-                    const int o = (int)tid + r * LZ_THREADS;
-                    if (o < lim && rawnx[r] >= lim && ((S.masks[o >> 5] >> (o & 31)) & 1u)) e = base + rawnx[r];
-                }
-                if (entry - base >= lim && tid == 0) e = entry;   // the whole tile lies inside one match
-                if (e >= 0) {
-                    uint32_t extra = 0;
-                    if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
-                    S.entry = (uint32_t)e; S.extra_lit = extra;
-                }
-            }
-            if (warp == 0) {
-                const uint32_t c0 = (uint32_t)__popc(S.masks[2 * lane]), c1 = (uint32_t)__popc(S.masks[2 * lane + 1]);
-                uint32_t incl = c0 + c1;
-                for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= (uint32_t)o) incl += v; }
-                S.seg_prefix[2 * lane] = incl - c0 - c1;
-                S.seg_prefix[2 * lane + 1] = incl - c1;
-                if (lane == 31) S.seg_prefix[TILE / 32] = incl;
-            }
-            PF(4);
-            __syncthreads();
-            // emission: 2 positions per thread
-            {
-                const uint32_t ntok0 = S.ntok;
-#pragma unroll
-                for (int r = 0; r < 2; r++) {
-                    uint32_t o = tid * 2u + (uint32_t)r;
-                    uint32_t seg = o >> 5, bit = o & 31u;
-                    uint32_t mk = S.masks[seg];
-                    if ((mk >> bit) & 1u) {
-                        uint32_t idx = ntok0 + S.seg_prefix[seg] + (uint32_t)__popc(mk & ((1u << bit) - 1u));
-                        uint32_t p = (uint32_t)(base + (int)o);
-                        bool lit; uint32_t step = parse_step(S, lp, p, n_s, lit);
-                        uint32_t tv;
-                        if (lit) { tv = ring_ld8(S.ring32, p); atomicAdd(&S.lfreq[tv], 1u); }
-                        else {
-                            uint32_t dist = (uint32_t)S.mdist[p & (MRING - 1)] + 1u;
-                            tv = tok_match(step, dist);
-                            atomicAdd(&S.lfreq[257u + len_code(step)], 1u);
-                            atomicAdd(&S.dfreq[dist_code(dist)], 1u);
-                        }
-                        tok[idx] = tv;
-                    }
-                }
-                if (tid == 0 && S.extra_lit) {
-                    uint32_t p = (uint32_t)(base + TILE);
-                    uint32_t tv = ring_ld8(S.ring32, p);
-                    atomicAdd(&S.lfreq[tv], 1u);
-                    tok[ntok0 + S.seg_prefix[TILE / 32]] = tv;
-                }
-            }
-            __syncthreads();
-            if (tid == 0) { S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0; }
-            __syncthreads();
-            PF(5);
+            PF(4);                                      // (BAR.SYNC is deferred-blocking: the wait shows up after the barrier)
+            pf[7]++;
         }
 
         // ---- chunk epilogue ----
-        flush_block(S, &brecs[S.blk], nc, tid);
+        flush_block(S, &brecs[S.blk], nc, tid, LZ_THREADS);
         if (tid == 0) {
             ChunkRec* cr = &chunks[c];
             cr->n_bytes = nc; cr->n_blocks = nblocks; cr->n_tokens = S.ntok;
-            for (int i = 0; i < 6; i++) atomicAdd(&g_lzprof[i], pf[i]);
-            atomicAdd(&g_lzprof[8], pf[8]); atomicAdd(&g_lzprof[9], pf[9]); atomicAdd(&g_lzprof[10], pf10);
+            atomicAdd(&g_lzprof[0], pf[0]); atomicAdd(&g_lzprof[2], pf[2]); atomicAdd(&g_lzprof[3], pf[3]);
+            atomicAdd(&g_lzprof[4], pf[4]); atomicAdd(&g_lzprof[7], pf[7]);
         }
-        if (tid == 64) { atomicAdd(&g_lzprof[6], pf[6]); atomicAdd(&g_lzprof[7], pf[7]); }
-        if (tid == 31 * 32) atomicAdd(&g_lzprof[0], pf31);
+        if (tid == 31 * 32) atomicAdd(&g_lzprof[8], pf[6]);
+        if (tid == 30 * 32) atomicAdd(&g_lzprof[9], pf[6]);
+        if (tid == 29 * 32) atomicAdd(&g_lzprof[10], pf[6]);
+        if (tid == 18 * 32) atomicAdd(&g_lzprof[1], pf[1]);
 #undef PF
     }
 }
