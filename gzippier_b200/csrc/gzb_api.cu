@@ -40,9 +40,12 @@ struct gzb_ctx {
     bool      pending = false;
     uint64_t  pending_n = 0;
     cudaStream_t pending_stream = nullptr;
-    // host path staging
-    uint8_t *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
-    uint64_t stage_in_cap = 0, stage_out_cap = 0;
+    // host path: two slots of device buffers (+ pinned staging, only used for pageable caller memory),
+    // copy streams and events for the H2D / kernels / D2H pipeline
+    uint8_t *h_in[2] = {nullptr, nullptr}, *h_out[2] = {nullptr, nullptr}, *d_in[2] = {nullptr, nullptr}, *d_out[2] = {nullptr, nullptr};
+    uint64_t dev_in_cap = 0, dev_out_cap = 0, pin_in_cap = 0, pin_out_cap = 0;
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t e_in[2] = {nullptr, nullptr}, e_cmp[2] = {nullptr, nullptr}, e_out[2] = {nullptr, nullptr};
     char      err[512];
     std::mutex mu;
 };
@@ -163,6 +166,8 @@ int gzb_create(int device, gzb_ctx** out)
     build_crc_tables(tab);
     memcpy(ctx->h_x2n, tab + 1024, sizeof(ctx->h_x2n));
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking) == cudaSuccess &&
               cudaMalloc(&ctx->d_tab, sizeof(tab)) == cudaSuccess &&
               cudaMemcpy(ctx->d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice) == cudaSuccess &&
               cudaMalloc(&ctx->d_cursor, sizeof(Cursor)) == cudaSuccess &&
@@ -170,6 +175,10 @@ int gzb_create(int device, gzb_ctx** out)
               cudaMalloc(&ctx->d_work, sizeof(uint32_t) * 65536) == cudaSuccess &&
               lz77_configure() == cudaSuccess;
     for (int i = 0; ok && i < MAX_SUB; i++) for (int j = 0; j < 6; j++) ok = ok && cudaEventCreate(&ctx->ev[i][j]) == cudaSuccess;
+    for (int i = 0; ok && i < 2; i++)
+        ok = cudaEventCreateWithFlags(&ctx->e_in[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->e_cmp[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->e_out[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { (void)cudaGetLastError(); gzb_destroy(ctx); return GZB_E_CUDA; }
     *out = ctx;
     return GZB_OK;
@@ -182,10 +191,19 @@ void gzb_destroy(gzb_ctx* ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->scr.tokens); cudaFree(ctx->scr.blocks); cudaFree(ctx->scr.chunks);
     cudaFree(ctx->d_tab); cudaFree(ctx->d_cursor); cudaFree(ctx->d_work);
-    cudaFree(ctx->d_in); cudaFree(ctx->d_out);
+    if (ctx->s_in) cudaStreamSynchronize(ctx->s_in);
+    if (ctx->s_out) cudaStreamSynchronize(ctx->s_out);
+    for (int i = 0; i < 2; i++) {
+        cudaFree(ctx->d_in[i]); cudaFree(ctx->d_out[i]);
+        if (ctx->h_in[i]) cudaFreeHost(ctx->h_in[i]);
+        if (ctx->h_out[i]) cudaFreeHost(ctx->h_out[i]);
+        if (ctx->e_in[i]) cudaEventDestroy(ctx->e_in[i]);
+        if (ctx->e_cmp[i]) cudaEventDestroy(ctx->e_cmp[i]);
+        if (ctx->e_out[i]) cudaEventDestroy(ctx->e_out[i]);
+    }
+    if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
+    if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
     if (ctx->h_cursor) cudaFreeHost(ctx->h_cursor);
-    if (ctx->h_in) cudaFreeHost(ctx->h_in);
-    if (ctx->h_out) cudaFreeHost(ctx->h_out);
     for (int i = 0; i < MAX_SUB; i++) for (int j = 0; j < 6; j++) if (ctx->ev[i][j]) cudaEventDestroy(ctx->ev[i][j]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     (void)cudaGetLastError();
@@ -340,36 +358,61 @@ int gzb_last_stage_ms(gzb_ctx* ctx, gzb_stage_ms* ms)
 // ---------------------------------------------------------------------------------------------
 namespace {
 
-int ensure_stage(gzb_ctx* ctx, uint64_t in_cap, uint64_t out_cap)
+int ensure_dev(gzb_ctx* ctx, uint64_t in_cap, uint64_t out_cap)
 {
-    if (ctx->stage_in_cap < in_cap) {
-        cudaFree(ctx->d_in); if (ctx->h_in) cudaFreeHost(ctx->h_in);
-        ctx->d_in = nullptr; ctx->h_in = nullptr; ctx->stage_in_cap = 0;
-        cudaError_t e;
-        if ((e = cudaMalloc(&ctx->d_in, in_cap)) != cudaSuccess || (e = cudaMallocHost(&ctx->h_in, in_cap)) != cudaSuccess) {
-            (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "staging (in)", e);
-        }
-        ctx->stage_in_cap = in_cap;
+    cudaError_t e = cudaSuccess;
+    if (ctx->dev_in_cap < in_cap) {
+        for (int i = 0; i < 2; i++) { cudaFree(ctx->d_in[i]); ctx->d_in[i] = nullptr; }
+        ctx->dev_in_cap = 0;
+        for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaMalloc(&ctx->d_in[i], in_cap);
+        if (e != cudaSuccess) { (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "device staging (in)", e); }
+        ctx->dev_in_cap = in_cap;
     }
-    if (ctx->stage_out_cap < out_cap) {
-        cudaFree(ctx->d_out); if (ctx->h_out) cudaFreeHost(ctx->h_out);
-        ctx->d_out = nullptr; ctx->h_out = nullptr; ctx->stage_out_cap = 0;
-        cudaError_t e;
-        if ((e = cudaMalloc(&ctx->d_out, out_cap)) != cudaSuccess || (e = cudaMallocHost(&ctx->h_out, out_cap)) != cudaSuccess) {
-            (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "staging (out)", e);
-        }
-        ctx->stage_out_cap = out_cap;
+    if (ctx->dev_out_cap < out_cap) {
+        for (int i = 0; i < 2; i++) { cudaFree(ctx->d_out[i]); ctx->d_out[i] = nullptr; }
+        ctx->dev_out_cap = 0;
+        for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaMalloc(&ctx->d_out[i], out_cap);
+        if (e != cudaSuccess) { (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "device staging (out)", e); }
+        ctx->dev_out_cap = out_cap;
     }
     return GZB_OK;
+}
+
+int ensure_pinned(gzb_ctx* ctx, uint64_t in_cap, uint64_t out_cap)
+{
+    cudaError_t e = cudaSuccess;
+    if (ctx->pin_in_cap < in_cap) {
+        for (int i = 0; i < 2; i++) { if (ctx->h_in[i]) cudaFreeHost(ctx->h_in[i]); ctx->h_in[i] = nullptr; }
+        ctx->pin_in_cap = 0;
+        for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaMallocHost(&ctx->h_in[i], in_cap);
+        if (e != cudaSuccess) { (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "pinned staging (in)", e); }
+        ctx->pin_in_cap = in_cap;
+    }
+    if (ctx->pin_out_cap < out_cap) {
+        for (int i = 0; i < 2; i++) { if (ctx->h_out[i]) cudaFreeHost(ctx->h_out[i]); ctx->h_out[i] = nullptr; }
+        ctx->pin_out_cap = 0;
+        for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaMallocHost(&ctx->h_out[i], out_cap);
+        if (e != cudaSuccess) { (void)cudaGetLastError(); return fail(ctx, GZB_E_NOMEM, "pinned staging (out)", e); }
+        ctx->pin_out_cap = out_cap;
+    }
+    return GZB_OK;
+}
+
+bool is_pinned(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
 }
 
 }  // namespace
 
 extern "C" {
 
-// Batches of HOST_BATCH bytes go through pinned staging: memcpy -> H2D -> kernels -> D2H -> memcpy.
-// (Round 1: one staging slot, copies and kernels serialised on the context's stream; the
-// double-buffered version is the next step -- DESIGN.md "Host path".)
+// Host buffers in, host buffers out.  The input is cut into batches of HOST_BATCH bytes that flow through a
+// three-stage pipeline on three streams -- H2D of batch i+1 || kernels of batch i || D2H of batch i-1 -- over two
+// slots of device buffers.  Pinned caller memory (cudaHostAlloc / cudaHostRegister / torch pin_memory) is DMA'd
+// directly; pageable memory goes through the context's pinned staging with one memcpy on each side.
 int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in, uint64_t n, const uint8_t* dict,
                      uint8_t* out, uint64_t out_cap, gzb_result* result)
 {
@@ -377,48 +420,77 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     if (level < 1 || level > 9) return fail(ctx, GZB_E_LEVEL, "level must be 1..9");
     if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
     const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
-    const uint32_t chunk = rs ? GZB_RSYNC_CHUNK : GZB_CHUNK, dsz = rs ? 0u : GZB_DICT;
-    const uint64_t HOST_BATCH = 256ull << 20;                      // multiple of both chunk sizes
+    const uint32_t dsz = rs ? 0u : GZB_DICT;
+    const uint64_t HOST_BATCH = 128ull << 20;                      // multiple of both chunk sizes
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU(ctx, cudaSetDevice(ctx->device));
+    const uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;
+    const uint64_t nbatch = n ? (n + HOST_BATCH - 1) / HOST_BATCH : 1;
+    const bool pin_in = n && is_pinned(in) && (!dict || is_pinned(dict)), pin_out = is_pinned(out);
+    int rc = ensure_dev(ctx, dsz + bmax + 16, gzb_bound(bmax, flags));
+    if (rc == GZB_OK) rc = ensure_pinned(ctx, pin_in ? 0 : dsz + bmax + 16, pin_out ? 0 : gzb_bound(bmax, flags));
+    if (rc != GZB_OK) return rc;
+
     gzb_result total; memset(&total, 0, sizeof(total));
     uint64_t opos = 0;
-    {
-        std::lock_guard<std::mutex> g(ctx->mu);
-        CU(ctx, cudaSetDevice(ctx->device));
-        uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;
-        int rc = ensure_stage(ctx, dsz + bmax + 16, gzb_bound(bmax, flags));
-        if (rc != GZB_OK) return rc;
-    }
-    uint64_t off = 0;
-    do {
-        const uint64_t nb = (n - off) < HOST_BATCH ? (n - off) : HOST_BATCH;
-        const bool lastb = off + nb == n;
-        // the 32 KiB before this batch: caller's dict for the first batch, the input itself afterwards
-        const uint8_t* halo_src = (off == 0) ? dict : in + off - dsz;
+    struct Pend { uint64_t bytes, opos; bool live; } pend[2] = {{0, 0, false}, {0, 0, false}};   // D2H in flight per slot
+
+    auto batch_len = [&](uint64_t i) { const uint64_t off = i * HOST_BATCH; return (n - off) < HOST_BATCH ? (n - off) : HOST_BATCH; };
+    auto issue_h2d = [&](uint64_t i) -> int {
+        const int sl = (int)(i & 1);
+        const uint64_t off = i * HOST_BATCH, nb = batch_len(i);
+        const uint8_t* halo_src = (off == 0) ? dict : in + off - dsz;       // the 32 KiB before the batch
         const uint32_t halo = (halo_src && dsz) ? dsz : 0u;
-        const uint32_t f = (flags & ~GZB_F_FINAL) | ((lastb && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
-        gzb_result r;
-        {
-            std::lock_guard<std::mutex> g(ctx->mu);
-            uint8_t* hin = ctx->h_in + (dsz - halo);               // keeps d_in + dsz 16-byte aligned
+        CU(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->e_cmp[sl], 0));        // kernels of batch i-2 have read this slot
+        uint8_t* dst = ctx->d_in[sl] + (dsz - halo);                        // keeps d_in + dsz 16-byte aligned
+        if (pin_in) {
+            if (off == 0) {
+                if (halo) CU(ctx, cudaMemcpyAsync(dst, halo_src, halo, cudaMemcpyHostToDevice, ctx->s_in));
+                if (nb) CU(ctx, cudaMemcpyAsync(dst + halo, in, nb, cudaMemcpyHostToDevice, ctx->s_in));
+            } else CU(ctx, cudaMemcpyAsync(dst, in + off - halo, halo + nb, cudaMemcpyHostToDevice, ctx->s_in));
+        } else {
+            CU(ctx, cudaEventSynchronize(ctx->e_in[sl]));                   // staging of batch i-2 has left the host
+            uint8_t* hin = ctx->h_in[sl] + (dsz - halo);
             if (halo) memcpy(hin, halo_src, halo);
             if (nb) memcpy(hin + halo, in + off, nb);
-            CU(ctx, cudaMemcpyAsync(ctx->d_in + (dsz - halo), hin, halo + nb, cudaMemcpyHostToDevice, ctx->stream));
+            CU(ctx, cudaMemcpyAsync(dst, hin, halo + nb, cudaMemcpyHostToDevice, ctx->s_in));
         }
-        int rc = gzb_deflate_device(ctx, level, f, ctx->d_in + dsz, nb, halo, ctx->d_out, ctx->stage_out_cap, &r, ctx->stream);
+        CU(ctx, cudaEventRecord(ctx->e_in[sl], ctx->s_in));
+        return GZB_OK;
+    };
+    auto drain = [&](int sl) -> int {                                      // complete the D2H of a slot
+        if (!pend[sl].live) return GZB_OK;
+        CU(ctx, cudaEventSynchronize(ctx->e_out[sl]));
+        if (!pin_out) memcpy(out + pend[sl].opos, ctx->h_out[sl], pend[sl].bytes);
+        pend[sl].live = false;
+        return GZB_OK;
+    };
+
+    if ((rc = issue_h2d(0)) != GZB_OK) return rc;
+    for (uint64_t i = 0; i < nbatch; i++) {
+        const int sl = (int)(i & 1);
+        const uint64_t off = i * HOST_BATCH, nb = batch_len(i);
+        const uint32_t halo = ((off == 0 ? dict != nullptr : true) && dsz) ? dsz : 0u;
+        const uint32_t f = (flags & ~GZB_F_FINAL) | ((i + 1 == nbatch && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
+        if ((rc = drain(sl)) != GZB_OK) return rc;                          // d_out[sl] / h_out[sl] are free again
+        CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->e_in[sl], 0));
+        rc = enqueue_deflate(ctx, level, f, ctx->d_in[sl] + dsz, nb, halo, ctx->d_out[sl], ctx->dev_out_cap, ctx->stream);
         if (rc != GZB_OK) return rc;
-        {
-            std::lock_guard<std::mutex> g(ctx->mu);
-            if (opos + r.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
-            CU(ctx, cudaMemcpyAsync(ctx->h_out, ctx->d_out, r.out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-            CU(ctx, cudaStreamSynchronize(ctx->stream));
-            memcpy(out + opos, ctx->h_out, r.out_bytes);
-        }
-        opos += r.out_bytes;
-        total.crc32 = gzb_crc32_combine(total.crc32, r.crc32, nb);
-        total.in_bytes += nb; total.n_chunks += r.n_chunks; total.n_blocks += r.n_blocks;
-        off += nb;
-        (void)chunk;
-    } while (off < n);
+        CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
+        if (i + 1 < nbatch && (rc = issue_h2d(i + 1)) != GZB_OK) return rc; // overlaps the kernels of batch i
+        CU(ctx, cudaStreamSynchronize(ctx->stream));                        // out_bytes of batch i is known now
+        const Cursor c = *ctx->h_cursor;
+        if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
+        if (c.in_bytes != nb) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
+        if (opos + c.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
+        if (c.out_bytes) CU(ctx, cudaMemcpyAsync(pin_out ? out + opos : ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));
+        CU(ctx, cudaEventRecord(ctx->e_out[sl], ctx->s_out));
+        pend[sl].bytes = c.out_bytes; pend[sl].opos = opos; pend[sl].live = true;
+        opos += c.out_bytes;
+        total.crc32 = gzb_crc32_combine(total.crc32, c.crc, nb);
+        total.in_bytes += nb; total.n_chunks += c.n_chunks; total.n_blocks += c.n_blocks;
+    }
+    for (int sl = 0; sl < 2; sl++) if ((rc = drain(sl)) != GZB_OK) return rc;
     total.out_bytes = opos; total.status = GZB_OK;
     if (result) *result = total;
     return GZB_OK;
@@ -461,19 +533,20 @@ int gzb_crc32_device(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, uint64_t n
 int gzb_crc32_host(gzb_ctx* ctx, uint32_t crc, const uint8_t* in, uint64_t n, uint32_t* crc_out)
 {
     if (!ctx || !crc_out || (n && !in)) return GZB_E_ARG;
-    const uint64_t B = 256ull << 20;
+    const uint64_t B = 128ull << 20;
     uint32_t acc = crc;
     for (uint64_t off = 0; off < n; off += B) {
         const uint64_t nb = (n - off) < B ? (n - off) : B;
         {
             std::lock_guard<std::mutex> g(ctx->mu);
             CU(ctx, cudaSetDevice(ctx->device));
-            int rc = ensure_stage(ctx, GZB_DICT + nb + 16, 0);
+            int rc = ensure_dev(ctx, GZB_DICT + nb + 16, 0);
+            if (rc == GZB_OK) rc = ensure_pinned(ctx, GZB_DICT + nb + 16, 0);
             if (rc != GZB_OK) return rc;
-            memcpy(ctx->h_in, in + off, nb);
-            CU(ctx, cudaMemcpyAsync(ctx->d_in, ctx->h_in, nb, cudaMemcpyHostToDevice, ctx->stream));
+            memcpy(ctx->h_in[0], in + off, nb);
+            CU(ctx, cudaMemcpyAsync(ctx->d_in[0], ctx->h_in[0], nb, cudaMemcpyHostToDevice, ctx->stream));
         }
-        int rc = gzb_crc32_device(ctx, acc, ctx->d_in, nb, &acc, ctx->stream);
+        int rc = gzb_crc32_device(ctx, acc, ctx->d_in[0], nb, &acc, ctx->stream);
         if (rc != GZB_OK) return rc;
     }
     *crc_out = acc;

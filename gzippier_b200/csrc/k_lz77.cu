@@ -166,16 +166,13 @@ __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, ui
         if (act) table[h] = (uint16_t)p16;
         __syncwarp();
         uint32_t todo = __ballot_sync(FULL, act && (uint32_t)table[h] != p16);
-        while (todo) {                                          // uniform; rare
-            const int leader = __ffs(todo) - 1;
-            const uint32_t hv = __shfl_sync(FULL, h, leader);
-            const uint32_t grp = __ballot_sync(FULL, h == hv);
-            if (h == hv) {
-                const uint32_t lower = grp & lt_mask;
+        if (todo) {                                             // uniform: some lanes of the step share a bucket
+            const uint32_t same = __match_any_sync(FULL, h);
+            if (act) {
+                const uint32_t lower = same & lt_mask;
                 if (lower) raw = (p16 - (lane - (uint32_t)(31 - __clz(lower)))) & 0xFFFFu;   // the nearest lower lane of the bucket
-                if ((grp >> lane) == 1u) table[h] = (uint16_t)p16;  // the last position of the step owns the bucket
+                if ((same >> lane) == 1u && lower) table[h] = (uint16_t)p16;               // the last position of the step owns the bucket
             }
-            todo &= ~grp;
         }
         if (act) { if (KIND == 0) S.link[slot_now] = (uint16_t)raw; else cx[i * 32u + lane] = (uint16_t)raw; }
         __syncwarp();
