@@ -162,11 +162,13 @@ __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, ui
         const bool act = (h & cmask) == cls;
         if (!act) h = 0xFFFFFFFFu;                              // never equal to a real bucket
         uint32_t raw = act ? (uint32_t)table[h] : 0u;
+        // write, read back, and only sort it out when a lane lost its bucket to another lane of the step
+        // (MATCH.ANY costs ~450 cycles: it is worth it only then)
         __syncwarp();
         if (act) table[h] = (uint16_t)p16;
         __syncwarp();
-        uint32_t todo = __ballot_sync(FULL, act && (uint32_t)table[h] != p16);
-        if (todo) {                                             // uniform: some lanes of the step share a bucket
+        const uint32_t todo = __ballot_sync(FULL, act && (uint32_t)table[h] != p16);
+        if (todo) {                                             // uniform
             const uint32_t same = __match_any_sync(FULL, h);
             if (act) {
                 const uint32_t lower = same & lt_mask;
@@ -326,8 +328,12 @@ __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in
 }
 
 // Token starts of tile k = the positions reachable from the entry point along next(), a pure function of the
-// per-position matches: pointer doubling over all positions of the tile (round r marks what is 2^r hops behind
-// a marked position).  Then every marked position emits its token; index = prefix popcount of the marks.
+// per-position matches.  Evaluated in three steps by the parser group:
+//   1. per 32-position window (one warp, lane = position): where does a parse that enters the window at this
+//      position leave it?  Pointer doubling with shuffles, 5 rounds.
+//   2. one thread hops from window to window along those exit functions: the entry position of every window.
+//   3. per entered window: the positions visited from its entry, again by doubling in registers -> mark bitmap.
+// Then every marked position emits its token; index = prefix popcount of the marks.
 __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t D, uint32_t n_s, uint32_t ntiles, uint32_t nblocks,
                                 uint32_t* __restrict__ tok, BlockRec* __restrict__ brecs, uint32_t gtid)
 {
@@ -346,50 +352,58 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
     }
     const int entry = (int)S.entry;                       // >= base by construction
     const int lim = hi_w - base;                          // positions [0, lim) of the tile can start a token
-    int rawnx[PPT];
+    constexpr int NWIN = TILE / 32, WPW = NWIN / PARSE_WARPS;
+    uint16_t* wexit = S.jump[0];                          // [o]: where the parse entering at o leaves o's window
+    uint16_t* went = S.jump[1];                           // [w]: entry position of window w, TILE = not entered
+    uint32_t jrel[WPW];                                   // next(o) relative to its window, 32 = leaves it
+    // 1.
 #pragma unroll
-    for (int r = 0; r < PPT; r++) {
-        const int o = (int)gtid + r * PG;
-        int nx = TILE;
+    for (int i = 0; i < WPW; i++) {
+        const int w = (int)warp + i * PARSE_WARPS, o = w * 32 + (int)lane;
+        int nx = TILE + 512;
         if (o < lim) { bool lit; uint32_t dd; nx = o + (int)parse_step(S, lp, (uint32_t)(base + o), n_s, lit, dd); }
-        rawnx[r] = nx;
-        if (o < TILE) S.jump[0][o] = (uint16_t)(nx < lim ? nx : TILE);
-    }
-    if (gtid < TILE / 32) S.masks[gtid] = (entry - base < lim && (uint32_t)(entry - base) / 32u == gtid) ? 1u << ((entry - base) & 31) : 0u;
-    group_sync();
-    for (int rd = 0;; rd++) {
-        const uint16_t* jc = S.jump[rd & 1]; uint16_t* jn = S.jump[(rd + 1) & 1];
-        bool more = false;
+        uint32_t j = (nx < lim && nx - w * 32 < 32) ? (uint32_t)(nx - w * 32) : 32u;
+        jrel[i] = j;
+        int x = nx;
 #pragma unroll
-        for (int r = 0; r < PPT; r++) {
-            const int o = (int)gtid + r * PG;
-            if (o < TILE) {
-                const uint32_t j = jc[o];
-                uint32_t jj = TILE;
-                if (j < (uint32_t)TILE) {
-                    if ((S.masks[o >> 5] >> (o & 31)) & 1u) { atomicOr(&S.masks[j >> 5], 1u << (j & 31u)); more = true; }
-                    jj = jc[j];
-                }
-                jn[o] = (uint16_t)jj;
+        for (int r = 0; r < 5; r++) {
+            const int xs = __shfl_sync(FULL, x, (int)(j & 31u));
+            const uint32_t js = __shfl_sync(FULL, j, (int)(j & 31u));
+            if (j < 32u) { x = xs; j = js; }
+        }
+        wexit[o] = (uint16_t)x;
+        if (lane == 0) went[w] = (uint16_t)TILE;
+    }
+    group_sync();
+    // 2.
+    if (gtid == 0) {
+        int e = entry - base;
+        while (e < lim) { went[e >> 5] = (uint16_t)e; e = wexit[e]; }
+        e += base;
+        uint32_t extra = 0;
+        if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
+        S.entry = (uint32_t)e; S.extra_lit = extra;
+    }
+    group_sync();
+    // 3.
+#pragma unroll
+    for (int i = 0; i < WPW; i++) {
+        const int w = (int)warp + i * PARSE_WARPS;
+        const uint32_t e = went[w];
+        uint32_t m = 0;
+        if (e < (uint32_t)TILE) {                           // uniform per warp
+            m = 1u << (e & 31u);
+            uint32_t j = jrel[i];
+#pragma unroll
+            for (int r = 0; r < 5; r++) {
+                m |= __reduce_or_sync(FULL, (((m >> lane) & 1u) && j < 32u) ? 1u << j : 0u);
+                const uint32_t js = __shfl_sync(FULL, j, (int)(j & 31u));
+                if (j < 32u) j = js;
             }
         }
-        if (!group_sync_or(more)) break;
+        if (lane == 0) S.masks[w] = m;
     }
-    // the marked position whose successor leaves the tile carries the entry point of the next tile
-    {
-        int e = -1;
-#pragma unroll
-        for (int r = 0; r < PPT; r++) {
-            const int o = (int)gtid + r * PG;
-            if (o < lim && rawnx[r] >= lim && ((S.masks[o >> 5] >> (o & 31)) & 1u)) e = base + rawnx[r];
-        }
-        if (entry - base >= lim && gtid == 0) e = entry;  // the whole tile lies inside one match
-        if (e >= 0) {
-            uint32_t extra = 0;
-            if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
-            S.entry = (uint32_t)e; S.extra_lit = extra;
-        }
-    }
+    group_sync();
     if (warp == 0) {
         const uint32_t c0 = (uint32_t)__popc(S.masks[2 * lane]), c1 = (uint32_t)__popc(S.masks[2 * lane + 1]);
         uint32_t incl = c0 + c1;
@@ -491,7 +505,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 pf[6] += (unsigned long long)(clock64() - c0);
             } else if (warp == 26) load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
             else if (do_parse && warp >= (uint32_t)PARSE_WARP0 && warp < (uint32_t)(PARSE_WARP0 + PARSE_WARPS))
-                parse_emit_tile(S, lp, k - 1, D, n_s, ntiles, nblocks, tok, brecs, tid - PARSE_WARP0 * 32u);
+            { long long c0 = clock64(); parse_emit_tile(S, lp, k - 1, D, n_s, ntiles, nblocks, tok, brecs, tid - PARSE_WARP0 * 32u); pf[6] += (unsigned long long)(clock64() - c0); }
             PF(1);
             if (do_search) {
                 for (;;) {
@@ -507,8 +521,10 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             __syncthreads();
             // all threads: the links of tile k+1 become final; 6-byte buckets of tile k+2; stash the match the next
             // parse needs from the slots the next search rewrites
+            long long c1 = clock64();
             if (do_insert) finish_tile(S, (uint32_t)(k + 1), n_s, tid);
             if (k + 2 < (int)ntiles) hash_tile(S, (uint32_t)(k + 2), tid);
+            pf[5] += (unsigned long long)(clock64() - c1);
             if (tid == 0) {
                 S.grp_ctr[0] = 0;
                 if (k >= 0) { const uint32_t cp = (uint32_t)k * TILE - 1u; S.carry_pos = cp; S.carry_len = S.mlen[cp & (MRING - 1)]; S.carry_dist = S.mdist[cp & (MRING - 1)]; }
@@ -530,7 +546,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         if (tid == 31 * 32) atomicAdd(&g_lzprof[8], pf[6]);
         if (tid == 30 * 32) atomicAdd(&g_lzprof[9], pf[6]);
         if (tid == 29 * 32) atomicAdd(&g_lzprof[10], pf[6]);
-        if (tid == 18 * 32) atomicAdd(&g_lzprof[1], pf[1]);
+        if (tid == 18 * 32) { atomicAdd(&g_lzprof[1], pf[1]); atomicAdd(&g_lzprof[11], pf[6]); }
+        if (tid == 0) atomicAdd(&g_lzprof[12], pf[5]);
 #undef PF
     }
 }

@@ -14,4 +14,4 @@ for level in (1, 6, 9):
     r = ctx.deflate_device(t_in, n, t_out, level)
     L.gzb_debug_lzprof(ctx._h, buf, 1)
     tiles = buf[7]
-    print(f"L{level} {kind} lz77 {ctx.stage_ms()['lz77']:.2f} ms ratio {n/r.out_bytes:.3f} | cycles per iteration: " + " ".join(f"{names[i]}={buf[i]/tiles:.0f}" for i in range(5)) + f" insert6={buf[8]/tiles:.0f} insert3={buf[9]/tiles:.0f} insert4={buf[10]/tiles:.0f}", flush=True)
+    print(f"L{level} {kind} lz77 {ctx.stage_ms()['lz77']:.2f} ms ratio {n/r.out_bytes:.3f} | cycles per iteration: " + " ".join(f"{names[i]}={buf[i]/tiles:.0f}" for i in range(5)) + f" insert6={buf[8]/tiles:.0f} insert3={buf[9]/tiles:.0f} insert4={buf[10]/tiles:.0f} pure_parse={buf[11]/tiles:.0f} pure_finish_hash={buf[12]/tiles:.0f}", flush=True)
