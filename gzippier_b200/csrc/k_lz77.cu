@@ -224,7 +224,7 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
     // "strictly longer wins" rule, so the result equals the one-candidate-at-a-time walk.
     constexpr int WALK_STEPS = 8;
     uint32_t limit = min((uint32_t)MAXD, p);
-    bool active = maxlen >= 3;
+    bool active = maxlen >= 6;                                  // the last five positions of a chunk walk no chain
     int nice = min(lp.nice, maxlen);
     int32_t slot = (int32_t)(p % LINK_RING);
     uint32_t delta = active ? (uint32_t)S.link[slot] : 0u;
@@ -334,11 +334,13 @@ __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in
 //   2. one thread hops from window to window along those exit functions: the entry position of every window.
 //   3. per entered window: the positions visited from its entry, again by doubling in registers -> mark bitmap.
 // Then every marked position emits its token; index = prefix popcount of the marks.
-__device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t D, uint32_t n_s, uint32_t ntiles, uint32_t nblocks,
-                                uint32_t* __restrict__ tok, BlockRec* __restrict__ brecs, uint32_t gtid)
+// D / n_s: stream positions where the tile's chunk starts / ends.  The last tile of a chunk also closes the chunk's
+// last block and its record, and resets the per-chunk counters for the next chunk of the run.
+__device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t D, uint32_t n_s, uint32_t nblocks,
+                                uint32_t* __restrict__ tok, BlockRec* __restrict__ brecs, ChunkRec* __restrict__ crec, uint32_t gtid)
 {
     const uint32_t lane = gtid & 31u, warp = gtid >> 5;
-    const bool last = (k == (int)ntiles - 1);
+    const bool last = ((uint32_t)(k + 1) * TILE >= n_s);
     const int base = k * TILE - 1;                        // decidable positions: [base, hi) (lazy needs mlen[p+1])
     const int hi = last ? (int)n_s : base + TILE;
     const int hi_w = min(hi, base + TILE);
@@ -443,10 +445,22 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
     }
     group_sync();
     if (gtid == 0) { S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0; }
+    if (last) {
+        group_sync();
+        flush_block(S, &brecs[S.blk], n_s - D, gtid, PG);
+        group_sync();
+        if (gtid == 0) {
+            crec->n_bytes = n_s - D; crec->n_blocks = nblocks; crec->n_tokens = S.ntok;
+            S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0;
+        }
+    }
 }
 
+// One CTA takes a RUN of `run` consecutive chunks and treats them as one stream: the hash tables and chains it has
+// at the end of a chunk are the next chunk's dictionary, so only the first chunk of a run pays for inserting its
+// 32 KiB dictionary (deflateSetDictionary) -- the parse, the tokens and the blocks stay per chunk.
 __global__ void __launch_bounds__(LZ_THREADS, 1)
-k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
+k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks, uint32_t run,
        uint32_t* __restrict__ tokens, BlockRec* __restrict__ blocks, ChunkRec* __restrict__ chunks, LevelParams lp,
        uint32_t* __restrict__ work_ctr)
 {
@@ -454,29 +468,28 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
     Smem& S = *reinterpret_cast<Smem*>(smem_raw);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
+    const uint32_t nruns = (nchunks + run - 1) / run;
 
     for (;;) {
         __syncthreads();
         if (tid == 0) S.chunk_idx = atomicAdd(work_ctr, 1u);
         __syncthreads();
-        const uint32_t c = S.chunk_idx;
-        if (c >= nchunks) break;
+        if (S.chunk_idx >= nruns) break;
+        const uint32_t c0 = S.chunk_idx * run;                                       // first chunk of the run
+        const uint32_t rc = min(run, nchunks - c0);                                  // chunks in the run
 
-        const uint64_t lo = (uint64_t)c * chunk;
-        const uint32_t nc = (uint32_t)min((uint64_t)chunk, n_bytes - lo);
+        const uint64_t lo = (uint64_t)c0 * chunk;
+        const uint32_t nr = (uint32_t)min((uint64_t)rc * chunk, n_bytes - lo);        // bytes of the run
         const uint32_t D = dict ? (uint32_t)min((uint64_t)dict, lo + halo) : 0u;
-        const uint8_t* sp = in + lo - D;                 // stream = dictionary || chunk
-        const uint32_t n_s = D + nc;
+        const uint8_t* sp = in + lo - D;                 // stream = dictionary || chunks of the run
+        const uint32_t n_s = D + nr;
         const uint32_t ntiles = (n_s + TILE - 1) / TILE;
         const uint32_t first_ctile = D / TILE;           // D is a multiple of TILE (0 or 32768)
-        const uint32_t nblocks = nc ? (nc + BLOCK_SPAN - 1) / BLOCK_SPAN : 1u;
-        uint32_t* tok = tokens + (size_t)c * chunk;
-        BlockRec* brecs = blocks + (size_t)c * bpc;
 
         unsigned long long pf[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         long long t0 = clock64(), t1;
 #define PF(i) do { t1 = clock64(); pf[i] += (unsigned long long)(t1 - t0); t0 = t1; } while (0)
-        // ---- per-chunk reset ----
+        // ---- per-run reset ----
         for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = 0;
         for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = 0;
         for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = 0;
@@ -505,16 +518,26 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 pf[6] += (unsigned long long)(clock64() - c0);
             } else if (warp == 26) load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
             else if (do_parse && warp >= (uint32_t)PARSE_WARP0 && warp < (uint32_t)(PARSE_WARP0 + PARSE_WARPS))
-            { long long c0 = clock64(); parse_emit_tile(S, lp, k - 1, D, n_s, ntiles, nblocks, tok, brecs, tid - PARSE_WARP0 * 32u); pf[6] += (unsigned long long)(clock64() - c0); }
+            {
+                long long cl0 = clock64();
+                const uint32_t ci = ((uint32_t)(k - 1) * TILE - D) / chunk;              // chunk of the run that tile k-1 belongs to
+                const uint32_t cs = D + ci * chunk, ce = min(cs + chunk, n_s);
+                const uint32_t ncb = ce - cs;
+                parse_emit_tile(S, lp, k - 1, cs, ce, (ncb + BLOCK_SPAN - 1) / BLOCK_SPAN, tokens + (size_t)(c0 + ci) * chunk,
+                                blocks + (size_t)(c0 + ci) * bpc, &chunks[c0 + ci], tid - PARSE_WARP0 * 32u);
+                pf[6] += (unsigned long long)(clock64() - cl0);
+            }
             PF(1);
             if (do_search) {
+                const uint32_t ci = ((uint32_t)k * TILE - D) / chunk;
+                const uint32_t ce = min(D + (ci + 1u) * chunk, n_s);                       // end of tile k's chunk
                 for (;;) {
                     uint32_t g = 0;
                     if (lane == 0) g = atomicAdd(&S.grp_ctr[0], 1u);
                     g = __shfl_sync(FULL, g, 0);
                     if (g >= (uint32_t)GROUPS_PER_TILE) break;
-                    if ((uint32_t)k * TILE + g * 32u >= n_s) continue;
-                    search_group(S, lp, (uint32_t)k, g, n_s, lane);
+                    if ((uint32_t)k * TILE + g * 32u >= ce) continue;
+                    search_group(S, lp, (uint32_t)k, g, ce, lane);
                 }
             }
             PF(2);
@@ -535,19 +558,15 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             pf[7]++;
         }
 
-        // ---- chunk epilogue ----
-        flush_block(S, &brecs[S.blk], nc, tid, LZ_THREADS);
+        // ---- run epilogue ----
         if (tid == 0) {
-            ChunkRec* cr = &chunks[c];
-            cr->n_bytes = nc; cr->n_blocks = nblocks; cr->n_tokens = S.ntok;
             atomicAdd(&g_lzprof[0], pf[0]); atomicAdd(&g_lzprof[2], pf[2]); atomicAdd(&g_lzprof[3], pf[3]);
-            atomicAdd(&g_lzprof[4], pf[4]); atomicAdd(&g_lzprof[7], pf[7]);
+            atomicAdd(&g_lzprof[4], pf[4]); atomicAdd(&g_lzprof[7], pf[7]); atomicAdd(&g_lzprof[12], pf[5]);
         }
         if (tid == 31 * 32) atomicAdd(&g_lzprof[8], pf[6]);
         if (tid == 30 * 32) atomicAdd(&g_lzprof[9], pf[6]);
         if (tid == 29 * 32) atomicAdd(&g_lzprof[10], pf[6]);
         if (tid == 18 * 32) { atomicAdd(&g_lzprof[1], pf[1]); atomicAdd(&g_lzprof[11], pf[6]); }
-        if (tid == 0) atomicAdd(&g_lzprof[12], pf[5]);
 #undef PF
     }
 }
@@ -569,9 +588,14 @@ cudaError_t lz77_configure()
 void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st)
 {
-    uint32_t grid = nchunks < (uint32_t)n_sm ? nchunks : (uint32_t)n_sm;
-    if (grid == 0) return;
-    k_lz77<<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, tokens, blocks, chunks, lp, work_ctr);
+    if (nchunks == 0) return;
+    // chunks per run: up to 4 when there are enough chunks to keep every SM busy for several runs; independent
+    // chunks (--rsyncable: no dictionary) are never chained
+    uint32_t run = 1;
+    if (dict) { run = nchunks / (4u * (uint32_t)n_sm); run = run < 1u ? 1u : run > 4u ? 4u : run; }
+    const uint32_t nruns = (nchunks + run - 1) / run;
+    const uint32_t grid = nruns < (uint32_t)n_sm ? nruns : (uint32_t)n_sm;
+    k_lz77<<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
 }
 
 }  // namespace gzb

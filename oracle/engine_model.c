@@ -101,7 +101,9 @@ void gzm_find_matches(const gzm_params *P, const uint8_t *s, int D, int n, uint1
         int best = 2, bdist = 0;
         int limit = p < P->maxd ? p : P->maxd;
         int nice = P->nice < maxlen ? P->nice : maxlen;
-        int c = link[p], depth = P->depth;
+        /* the last five positions of a chunk, whose six hashed bytes would run past its end, do not walk a chain
+         * (what follows the chunk is the next chunk's business: the engine may or may not have it at hand) */
+        int c = maxlen >= 6 ? link[p] : -1, depth = P->depth;
         while (c >= 0 && p - c <= limit && depth-- > 0) {
             if (maxlen > best && s[c + best] == s[p + best]) {
                 int l = common_len(s + c, s + p, maxlen);
