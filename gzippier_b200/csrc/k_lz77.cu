@@ -162,18 +162,34 @@ __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, ui
         const bool act = (h & cmask) == cls;
         if (!act) h = 0xFFFFFFFFu;                              // never equal to a real bucket
         uint32_t raw = act ? (uint32_t)table[h] : 0u;
-        // write, read back, and only sort it out when a lane lost its bucket to another lane of the step
-        // (MATCH.ANY costs ~450 cycles: it is worth it only then)
+        // Write, read back: a lane that does not find its own position shares its bucket with another lane of the step.
+        // The losers then write once more: a bucket shared by exactly TWO lanes -- the usual case -- is settled by these
+        // two exchanges (each lane has read the other's position); only buckets with three or more lanes of the step
+        // need MATCH.ANY (~450 cycles).
         __syncwarp();
         if (act) table[h] = (uint16_t)p16;
         __syncwarp();
-        const uint32_t todo = __ballot_sync(FULL, act && (uint32_t)table[h] != p16);
-        if (todo) {                                             // uniform
-            const uint32_t same = __match_any_sync(FULL, h);
-            if (act) {
-                const uint32_t lower = same & lt_mask;
-                if (lower) raw = (p16 - (lane - (uint32_t)(31 - __clz(lower)))) & 0xFFFFu;   // the nearest lower lane of the bucket
-                if ((same >> lane) == 1u && lower) table[h] = (uint16_t)p16;               // the last position of the step owns the bucket
+        const uint32_t r1 = act ? (uint32_t)table[h] : p16;
+        const bool lost = r1 != p16;
+        if (__ballot_sync(FULL, lost)) {                         // uniform
+            __syncwarp();
+            if (lost) table[h] = (uint16_t)p16;
+            __syncwarp();
+            const uint32_t r2 = act ? (uint32_t)table[h] : p16;
+            if (__ballot_sync(FULL, lost && r2 != p16) == 0u) {
+                const bool paired = lost || r2 != p16;
+                const uint32_t partner = lost ? r1 : r2;
+                const bool partner_lower = ((p16 - partner) & 0xFFFFu) < 32u;
+                if (paired && partner_lower) raw = partner;                  // the other lane of the bucket precedes me
+                __syncwarp();
+                if (paired && partner_lower && !lost) table[h] = (uint16_t)p16;   // the later position owns the bucket
+            } else {
+                const uint32_t same = __match_any_sync(FULL, h);
+                if (act) {
+                    const uint32_t lower = same & lt_mask;
+                    if (lower) raw = (p16 - (lane - (uint32_t)(31 - __clz(lower)))) & 0xFFFFu;   // the nearest lower lane of the bucket
+                    if ((same >> lane) == 1u && lower) table[h] = (uint16_t)p16;               // the last position of the step owns the bucket
+                }
             }
         }
         if (act) { if (KIND == 0) S.link[slot_now] = (uint16_t)raw; else cx[i * 32u + lane] = (uint16_t)raw; }
@@ -234,7 +250,8 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
     while (__any_sync(FULL, active)) {
         uint32_t pend0 = 0, pend1 = 0;
 #pragma unroll 1
-        for (int st = 0; st < WALK_STEPS; st++) {
+        for (int st = 0; st < lp.walk_steps; st++) {
+            if (lp.walk_exit && !__any_sync(FULL, active && pend1 == 0u)) break;
             if (active && pend1 == 0u) {
                 if (delta == 0u || depth == 0) active = false;
                 else {
