@@ -1,22 +1,31 @@
 // k_lz77.cu -- LZ77 match finding + greedy/lazy parse + literal/length/distance histograms.
 //
-// Replaces, for one chunk per CTA: deflateSetDictionary (lib/zlib/deflate.c:376-442),
+// Replaces, for a run of chunks per CTA: deflateSetDictionary (lib/zlib/deflate.c:376-442),
 // INSERT_STRING (:182-185), longest_match (:1236-1377), deflate_fast (:1824-1918),
 // deflate_slow (:1926-2049) and _tr_tally (deflate.h:326-342).  Not a port: zlib walks one
-// position at a time and skips positions inside matches; here EVERY position of a 2 KiB tile is
-// searched in parallel (one thread per position) against hash chains that an "inserter" warp
-// builds in exact stream order one tile ahead, and the greedy/lazy parse is then a pure
-// function next(p) of the per-position results, evaluated by a speculative parallel walk.
+// position at a time and skips positions inside matches.  Here EVERY position is inserted, in
+// exact stream order, into hash chains keyed on 6 bytes (plus single-entry 4-byte and 3-byte
+// tables), which makes match(p) a pure function of the data; every position of a 2 KiB tile is
+// searched in parallel (one lane per position), and the greedy/lazy parse -- a pure function
+// next(p) of the per-position matches -- is evaluated with pointer doubling instead of a walk.
 //
-// One persistent CTA (1024 threads, ~200 KB shared memory) per SM, chunks handed out by an
-// atomic counter.  Shared memory holds the whole search state of the chunk:
-//   ring   64 KiB  window bytes, stream position & 0xFFFF  (dictionary + chunk stream)
+// One persistent CTA (1024 threads, ~226 KB shared memory) per SM takes runs of up to 4
+// consecutive chunks from an atomic counter and streams through them: the tables at the end of
+// a chunk ARE the next chunk's dictionary, so only the first chunk of a run inserts its 32 KiB
+// dictionary.  Per tile k the CTA runs three things at once (one barrier per tile):
+//   warps 29-31  insert tile k+1 into the three tables: the serial part only (head exchange)
+//   warps 18-25  parse + emit tile k-1 (tokens, histograms, block / chunk records)
+//   all others   search tile k in 32-position groups handed out dynamically; everybody joins
+//                when its own role is done, then turns tile k+1's raw heads into links
+// Shared memory holds the whole search state:
+//   ring   64 KiB  window bytes, stream position & 0xFFFF
 //   link   72 KiB  u16 delta to the previous position in the same 6-byte bucket (0 = none),
 //                  indexed by stream position mod LINK_RING; deltas need no sliding
 //   head   32 KiB  u16 last position (mod 64 Ki) per 6-byte bucket -- inserter-private
 //   head3/4 8+8 KiB u16 last position per 3-byte / 4-byte bucket (single entry, no chain)
 //   c3/c4  8+8 KiB per-position delta to the most recent 3-byte / 4-byte twin, double-buffered per tile
 //   mlen/mdist 12 KiB  per-position best match of the last two tiles
+//   jump    8 KiB  parse scratch (window exit functions)
 // Stale/aliased head entries are detected by re-hashing the bytes at the candidate, which makes
 // the chains exactly "all earlier positions of the same bucket, most recent first"
 // (oracle/engine_model.c is the sequential statement of the same semantics).
@@ -24,8 +33,8 @@
 
 namespace gzb {
 
-// cycle counters of the pipeline phases (thread 0 = inserter warp, thread 32 = a searcher warp), summed over CTAs:
-// 0 insert, 1 load, 2 warp0 search, 3 warp0 wait A, 4 walk, 5 emit+syncs, 6 warp1 search, 7 warp1 wait A, 8 chunk setup, 9 tiles
+// cycle counters (debugging aid, tools/lzprof.py), summed over CTAs: 7 pipeline iterations, 8-10 time in insert_tile of the
+// 6-byte / 3-byte / 4-byte table warp, 11 time in parse_emit_tile (thread 0 of the parser group)
 __device__ unsigned long long g_lzprof[16];
 
 namespace {
@@ -51,7 +60,9 @@ struct Smem {
     uint32_t masks[TILE / 32];            // token-start bitmap of the tile being parsed
     uint32_t seg_prefix[TILE / 32 + 1];
     uint16_t jump[2][TILE];               // pointer doubling: 2^r-th successor of every position (TILE = leaves the tile)
-    uint32_t grp_ctr[2];                  // dynamic group scheduler of the search phase
+    uint32_t grp_ctr[2];                  // dynamic group scheduler of the search phase (alternating per iteration, like the next two)
+    uint32_t post_ctr[2];                 // ... of the finish/hash work that follows it
+    uint32_t ins_done[2];                 // inserter + loader warps that have finished their part of the iteration
     uint32_t chunk_idx;
     uint32_t entry;                       // next token start (stream position)
     uint32_t ntok;                        // tokens emitted so far in this chunk
@@ -130,16 +141,18 @@ __device__ __forceinline__ uint32_t bucket_of(uint32_t v, uint32_t v2)
     return KIND == 0 ? hash6(v, v2 & 0xFFFFu) : KIND == 1 ? hash3(v) : hash4(v);
 }
 
-__device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
+__device__ __forceinline__ void hash_pos(Smem& S, uint32_t t, uint32_t o)
 {
     // the bucket of a position is parked where its link / c3 / c4 entry will go: those slots are dead until insertion
+    const uint32_t p = t * TILE + o;
+    const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);      // zero past the end of the stream
+    uint32_t slot = (t * TILE) % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
+    S.link[slot] = (uint16_t)bucket_of<0>(v, v2); S.c3[t & 1][o] = (uint16_t)bucket_of<1>(v, v2); S.c4[t & 1][o] = (uint16_t)bucket_of<2>(v, v2);
+}
+__device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
+{
 #pragma unroll
-    for (int j = 0; j < TILE / LZ_THREADS; j++) {
-        const uint32_t o = tid + (uint32_t)j * LZ_THREADS, p = t * TILE + o;
-        const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);      // zero past the end of the stream
-        uint32_t slot = (t * TILE) % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
-        S.link[slot] = (uint16_t)bucket_of<0>(v, v2); S.c3[t & 1][o] = (uint16_t)bucket_of<1>(v, v2); S.c4[t & 1][o] = (uint16_t)bucket_of<2>(v, v2);
-    }
+    for (int j = 0; j < TILE / LZ_THREADS; j++) hash_pos(S, t, tid + (uint32_t)j * LZ_THREADS);
 }
 
 // cls / cmask: only the buckets with (bucket & cmask) == cls are inserted (0, 0 = all).
@@ -197,31 +210,27 @@ __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, ui
     }
 }
 
-__device__ void finish_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t tid)
+__device__ __forceinline__ void finish_pos(Smem& S, uint32_t t, uint32_t n_s, uint32_t o)
 {
-    const uint32_t base = t * TILE;
-#pragma unroll
-    for (int j = 0; j < TILE / LZ_THREADS; j++) {
-        const uint32_t o = tid + (uint32_t)j * LZ_THREADS, p = base + o;
-        if (p >= n_s) continue;
-        const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);
-        uint32_t slot = base % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
-        {
-            const uint32_t d = (p - (uint32_t)S.link[slot]) & 0xFFFFu;
-            const bool ok = d != 0u && d <= 32767u && d <= p;
-            const uint32_t c = ok ? p - d : p;
-            S.link[slot] = (uint16_t)((ok && bucket_of<0>(ring_ld32(S.ring32, c), ring_ld32(S.ring32, c + 4u)) == bucket_of<0>(v, v2)) ? d : 0u);
-        }
-        {
-            const uint32_t d = (p - (uint32_t)S.c3[t & 1][o]) & 0xFFFFu;
-            const bool ok = d != 0u && d <= (uint32_t)TOO_FAR && d <= p;
-            S.c3[t & 1][o] = (uint16_t)((ok && hash3(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash3(v)) ? d : 0u);
-        }
-        {
-            const uint32_t d = (p - (uint32_t)S.c4[t & 1][o]) & 0xFFFFu;
-            const bool ok = d != 0u && d <= 32767u && d <= p;
-            S.c4[t & 1][o] = (uint16_t)((ok && hash4(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash4(v)) ? d : 0u);
-        }
+    const uint32_t base = t * TILE, p = base + o;
+    if (p >= n_s) return;
+    const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);
+    uint32_t slot = base % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
+    {
+        const uint32_t d = (p - (uint32_t)S.link[slot]) & 0xFFFFu;
+        const bool ok = d != 0u && d <= 32767u && d <= p;
+        const uint32_t c = ok ? p - d : p;
+        S.link[slot] = (uint16_t)((ok && bucket_of<0>(ring_ld32(S.ring32, c), ring_ld32(S.ring32, c + 4u)) == bucket_of<0>(v, v2)) ? d : 0u);
+    }
+    {
+        const uint32_t d = (p - (uint32_t)S.c3[t & 1][o]) & 0xFFFFu;
+        const bool ok = d != 0u && d <= (uint32_t)TOO_FAR && d <= p;
+        S.c3[t & 1][o] = (uint16_t)((ok && hash3(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash3(v)) ? d : 0u);
+    }
+    {
+        const uint32_t d = (p - (uint32_t)S.c4[t & 1][o]) & 0xFFFFu;
+        const bool ok = d != 0u && d <= 32767u && d <= p;
+        S.c4[t & 1][o] = (uint16_t)((ok && hash4(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash4(v)) ? d : 0u);
     }
 }
 
@@ -461,7 +470,13 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
         }
     }
     group_sync();
-    if (gtid == 0) { S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0; }
+    if (gtid == 0) {
+        S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0;
+        // the parse of the next tile starts at this tile's last position, whose slot in mlen/mdist the search that runs
+        // beside it rewrites: stash it now
+        const uint32_t cp = (uint32_t)(k + 1) * TILE - 1u;
+        S.carry_pos = cp; S.carry_len = S.mlen[cp & (MRING - 1)]; S.carry_dist = S.mdist[cp & (MRING - 1)];
+    }
     if (last) {
         group_sync();
         flush_block(S, &brecs[S.blk], n_s - D, gtid, PG);
@@ -504,38 +519,44 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         const uint32_t first_ctile = D / TILE;           // D is a multiple of TILE (0 or 32768)
 
         unsigned long long pf[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        long long t0 = clock64(), t1;
-#define PF(i) do { t1 = clock64(); pf[i] += (unsigned long long)(t1 - t0); t0 = t1; } while (0)
         // ---- per-run reset ----
         for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = 0;
         for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = 0;
         for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = 0;
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
-        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[0] = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
+        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[1] = 0; S.post_ctr[1] = 0; S.ins_done[1] = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
         for (uint32_t t = 0; t < 3; t++) load_tile(S, sp, n_s, t, tid, LZ_THREADS);
         __syncthreads();
         hash_tile(S, 0u, tid);
         __syncthreads();
-        PF(0);
 
         // ---- pipeline: iteration k inserts tile k+1, searches tile k and parses + emits tile k-1, all at once ----
         for (int k = -1; k <= (int)ntiles; k++) {
             const bool do_insert = k + 1 < (int)ntiles;
+            const bool do_hash = k + 2 < (int)ntiles;
             const bool do_parse = k - 1 >= (int)first_ctile;                      // k - 1 < ntiles by the loop bound
             const bool do_search = k >= (int)first_ctile && k < (int)ntiles;
+            const uint32_t par = (uint32_t)k & 1u;
+            if (tid == 0) { S.grp_ctr[par ^ 1u] = 0; S.post_ctr[par ^ 1u] = 0; S.ins_done[par ^ 1u] = 0; }   // next iteration's counters
             // roles: three serial inserter warps (raw heads), one loader, eight parser warps; everybody else -- and
             // everybody who is done -- searches
-            if (do_insert && warp >= 29) {
-                long long c0 = clock64();
-                const uint32_t t = (uint32_t)(k + 1);
-                if (warp == 31) insert_tile<0>(S, t, n_s, lane, 0u, 0u);
-                else if (warp == 30) insert_tile<1>(S, t, n_s, lane, 0u, 0u);
-                else insert_tile<2>(S, t, n_s, lane, 0u, 0u);
-                pf[6] += (unsigned long long)(clock64() - c0);
-            } else if (warp == 26) load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
-            else if (do_parse && warp >= (uint32_t)PARSE_WARP0 && warp < (uint32_t)(PARSE_WARP0 + PARSE_WARPS))
-            {
+            if (warp >= 29) {
+                if (do_insert) {
+                    long long c0 = clock64();
+                    const uint32_t t = (uint32_t)(k + 1);
+                    if (warp == 31) insert_tile<0>(S, t, n_s, lane, 0u, 0u);
+                    else if (warp == 30) insert_tile<1>(S, t, n_s, lane, 0u, 0u);
+                    else insert_tile<2>(S, t, n_s, lane, 0u, 0u);
+                    pf[6] += (unsigned long long)(clock64() - c0);
+                }
+                __syncwarp();
+                if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_done[par], 1u); }
+            } else if (warp == 26) {
+                load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
+                __syncwarp();
+                if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_done[par], 1u); }
+            } else if (do_parse && warp >= (uint32_t)PARSE_WARP0 && warp < (uint32_t)(PARSE_WARP0 + PARSE_WARPS)) {
                 long long cl0 = clock64();
                 const uint32_t ci = ((uint32_t)(k - 1) * TILE - D) / chunk;              // chunk of the run that tile k-1 belongs to
                 const uint32_t cs = D + ci * chunk, ce = min(cs + chunk, n_s);
@@ -544,47 +565,46 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                                 blocks + (size_t)(c0 + ci) * bpc, &chunks[c0 + ci], tid - PARSE_WARP0 * 32u);
                 pf[6] += (unsigned long long)(clock64() - cl0);
             }
-            PF(1);
             if (do_search) {
                 const uint32_t ci = ((uint32_t)k * TILE - D) / chunk;
                 const uint32_t ce = min(D + (ci + 1u) * chunk, n_s);                       // end of tile k's chunk
                 for (;;) {
                     uint32_t g = 0;
-                    if (lane == 0) g = atomicAdd(&S.grp_ctr[0], 1u);
+                    if (lane == 0) g = atomicAdd(&S.grp_ctr[par], 1u);
                     g = __shfl_sync(FULL, g, 0);
                     if (g >= (uint32_t)GROUPS_PER_TILE) break;
                     if ((uint32_t)k * TILE + g * 32u >= ce) continue;
                     search_group(S, lp, (uint32_t)k, g, ce, lane);
                 }
             }
-            PF(2);
-            __syncthreads();
-            // all threads: the links of tile k+1 become final; 6-byte buckets of tile k+2; stash the match the next
-            // parse needs from the slots the next search rewrites
-            long long c1 = clock64();
-            if (do_insert) finish_tile(S, (uint32_t)(k + 1), n_s, tid);
-            if (k + 2 < (int)ntiles) hash_tile(S, (uint32_t)(k + 2), tid);
-            pf[5] += (unsigned long long)(clock64() - c1);
-            if (tid == 0) {
-                S.grp_ctr[0] = 0;
-                if (k >= 0) { const uint32_t cp = (uint32_t)k * TILE - 1u; S.carry_pos = cp; S.carry_len = S.mlen[cp & (MRING - 1)]; S.carry_dist = S.mdist[cp & (MRING - 1)]; }
+            // whoever runs out of work turns the raw heads of tile k+1 into final links, 32 positions at a time, as soon
+            // as the inserters are through
+            if (do_insert) {
+                while (*(volatile uint32_t*)&S.ins_done[par] < 4u) __nanosleep(250);
+                __threadfence_block();
+                for (;;) {
+                    uint32_t g = 0;
+                    if (lane == 0) g = atomicAdd(&S.post_ctr[par], 1u);
+                    g = __shfl_sync(FULL, g, 0);
+                    if (g >= (uint32_t)GROUPS_PER_TILE) break;
+                    finish_pos(S, (uint32_t)(k + 1), n_s, g * 32u + lane);
+                }
             }
-            PF(3);
             __syncthreads();
-            PF(4);                                      // (BAR.SYNC is deferred-blocking: the wait shows up after the barrier)
+            // the buckets of tile k+2 are parked in slots that the search of tile k was still reading
+            if (do_hash) hash_tile(S, (uint32_t)(k + 2), tid);
+            __syncthreads();
             pf[7]++;
         }
 
         // ---- run epilogue ----
         if (tid == 0) {
-            atomicAdd(&g_lzprof[0], pf[0]); atomicAdd(&g_lzprof[2], pf[2]); atomicAdd(&g_lzprof[3], pf[3]);
-            atomicAdd(&g_lzprof[4], pf[4]); atomicAdd(&g_lzprof[7], pf[7]); atomicAdd(&g_lzprof[12], pf[5]);
+            atomicAdd(&g_lzprof[7], pf[7]);
         }
         if (tid == 31 * 32) atomicAdd(&g_lzprof[8], pf[6]);
         if (tid == 30 * 32) atomicAdd(&g_lzprof[9], pf[6]);
         if (tid == 29 * 32) atomicAdd(&g_lzprof[10], pf[6]);
-        if (tid == 18 * 32) { atomicAdd(&g_lzprof[1], pf[1]); atomicAdd(&g_lzprof[11], pf[6]); }
-#undef PF
+        if (tid == 18 * 32) atomicAdd(&g_lzprof[11], pf[6]);
     }
 }
 
