@@ -232,8 +232,6 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     const uint64_t nchunks64 = (n + chunk - 1) / chunk;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     LevelParams lp = level_params(level);
-    lp.walk_steps = getenv("GZB_WALK") ? atoi(getenv("GZB_WALK")) : (level <= 6 ? 4 : 8);
-    lp.walk_exit = getenv("GZB_WEXIT") ? atoi(getenv("GZB_WEXIT")) : 0;
     ctx->n_sub_timed = 0;
 
     CU(ctx, cudaMemsetAsync(ctx->d_cursor, 0, sizeof(Cursor), st));

@@ -13,13 +13,13 @@
 // consecutive chunks from an atomic counter and streams through them: the tables at the end of
 // a chunk ARE the next chunk's dictionary, so only the first chunk of a run inserts its 32 KiB
 // dictionary.  Per tile k the CTA runs three things at once (one barrier per tile):
-//   warps 29-31  insert tile k+1 into the three tables: the serial part only (head exchange)
-//   warps 18-25  parse + emit tile k-1 (tokens, histograms, block / chunk records)
+//   3 warps      insert tile k+1 into the three tables: the serial part only (head exchange)
+//   8 warps      parse + emit tile k-1 (tokens, histograms, block / chunk records)
 //   all others   search tile k in 32-position groups handed out dynamically; everybody joins
 //                when its own role is done, then turns tile k+1's raw heads into links
 // Shared memory holds the whole search state:
 //   ring   64 KiB  window bytes, stream position & 0xFFFF
-//   link   72 KiB  u16 delta to the previous position in the same 6-byte bucket (0 = none),
+//   link   72 KiB  u16 delta to the previous position in the same 6-byte bucket (0xFFFF = none),
 //                  indexed by stream position mod LINK_RING; deltas need no sliding
 //   head   32 KiB  u16 last position (mod 64 Ki) per 6-byte bucket -- inserter-private
 //   head3/4 8+8 KiB u16 last position per 3-byte / 4-byte bucket (single entry, no chain)
@@ -42,7 +42,7 @@ namespace {
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 constexpr uint32_t NOPOS = 0xFFFFFFFFu;
 constexpr int GROUPS_PER_TILE = TILE / 32;
-constexpr int RING_MIRROR = 272;         // >= 258 + 3 (longest compare) + 4, multiple of 16
+constexpr int RING_MIRROR = 288;         // >= 258 + 3 + 19 (longest compare, see match_len_s) + 4, multiple of 16
 constexpr int MRING = 2 * TILE;           // per-position match results kept for two tiles
 
 struct Smem {
@@ -85,20 +85,30 @@ __device__ __forceinline__ uint32_t ring_ld8(const uint32_t* ring32, uint32_t po
     return reinterpret_cast<const uint8_t*>(ring32)[pos & 0xFFFFu];
 }
 
-// length of the common prefix of the strings at stream positions p and c, at most maxlen (>= 1)
-__device__ __forceinline__ int match_len(const uint32_t* ring32, uint32_t p, uint32_t c, int maxlen)
+// The search loop addresses shared memory by 32-bit shared-space address: one IADD per access, no generic-pointer
+// arithmetic, and the compiler has nothing to re-derive inside the loop.
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a)  { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+template <int OFF>
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFF)); return v; }
+
+// Length of the common prefix of the strings at stream positions p and c, at most maxlen (>= 1); four words per trip
+// (reads up to 19 bytes past maxlen: RING_MIRROR covers it).
+__device__ __forceinline__ int match_len_s(uint32_t ring_s, uint32_t p, uint32_t c, int maxlen)
 {
     const uint32_t ap = p & 0xFFFFu, ac = c & 0xFFFFu;
-    const uint32_t* wp = ring32 + (ap >> 2);
-    const uint32_t* wc = ring32 + (ac >> 2);
+    uint32_t wp = ring_s + (ap & 0xFFFCu), wc = ring_s + (ac & 0xFFFCu);
     const uint32_t sp = (ap & 3u) * 8u, sc = (ac & 3u) * 8u;
-    uint32_t p0 = wp[0], c0 = wc[0];
-    const int nw = (maxlen + 3) >> 2;
-    for (int k = 1; k <= nw; k++) {
-        const uint32_t p1 = wp[k], c1 = wc[k];
-        const uint32_t x = __funnelshift_r(p0, p1, sp) ^ __funnelshift_r(c0, c1, sc);
-        if (x) return min(maxlen, 4 * (k - 1) + ((__ffs(x) - 1) >> 3));
+    uint32_t p0 = lds_u32<0>(wp), c0 = lds_u32<0>(wc);
+    for (int done = 0; done < maxlen; done += 16, wp += 16u, wc += 16u) {
+        uint32_t p1, c1, x;
+#define GZB_ML_STEP(K)                                                                        \
+        p1 = lds_u32<4 * (K) + 4>(wp); c1 = lds_u32<4 * (K) + 4>(wc);                          \
+        x = __funnelshift_r(p0, p1, sp) ^ __funnelshift_r(c0, c1, sc);                        \
+        if (x) return min(maxlen, done + 4 * (K) + ((__ffs(x) - 1) >> 3));                    \
         p0 = p1; c0 = c1;
+        GZB_ML_STEP(0) GZB_ML_STEP(1) GZB_ML_STEP(2) GZB_ML_STEP(3)
+#undef GZB_ML_STEP
     }
     return maxlen;
 }
@@ -220,7 +230,7 @@ __device__ __forceinline__ void finish_pos(Smem& S, uint32_t t, uint32_t n_s, ui
         const uint32_t d = (p - (uint32_t)S.link[slot]) & 0xFFFFu;
         const bool ok = d != 0u && d <= 32767u && d <= p;
         const uint32_t c = ok ? p - d : p;
-        S.link[slot] = (uint16_t)((ok && bucket_of<0>(ring_ld32(S.ring32, c), ring_ld32(S.ring32, c + 4u)) == bucket_of<0>(v, v2)) ? d : 0u);
+        S.link[slot] = (uint16_t)((ok && bucket_of<0>(ring_ld32(S.ring32, c), ring_ld32(S.ring32, c + 4u)) == bucket_of<0>(v, v2)) ? d : 0xFFFFu);
     }
     {
         const uint32_t d = (p - (uint32_t)S.c3[t & 1][o]) & 0xFFFFu;
@@ -235,7 +245,7 @@ __device__ __forceinline__ void finish_pos(Smem& S, uint32_t t, uint32_t n_s, ui
 }
 
 // Best match for the 32 positions of one group (one warp).  Semantics: engine_model.c gzm_find_matches.
-__device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_t g, uint32_t n_s, uint32_t lane)
+__device__ void search_group(Smem& S, uint32_t sbase, const LevelParams& lp, uint32_t t, uint32_t g, uint32_t n_s, uint32_t lane)
 {
     uint32_t p = t * TILE + g * 32u + lane;
     int maxlen = (p < n_s) ? min(258, (int)(n_s - p)) : 0;
@@ -247,46 +257,47 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
     // Filtering in A uses the best length as of the last B, which is a weaker (still necessary)
     // condition; B re-applies the exact filter.  Candidates are judged in chain order with the
     // "strictly longer wins" rule, so the result equals the one-candidate-at-a-time walk.
-    constexpr int WALK_STEPS = 8;
-    uint32_t limit = min((uint32_t)MAXD, p);
-    bool active = maxlen >= 6;                                  // the last five positions of a chunk walk no chain
-    int nice = min(lp.nice, maxlen);
-    int32_t slot = (int32_t)(p % LINK_RING);
-    uint32_t delta = active ? (uint32_t)S.link[slot] : 0u;
+    constexpr int WALK_STEPS = 4;
+    const uint32_t ring_s = sbase + (uint32_t)offsetof(Smem, ring32), link_s = sbase + (uint32_t)offsetof(Smem, link);
+    const uint32_t limit = min((uint32_t)MAXD, p);
+    const int nice = min(lp.nice, maxlen);
+    constexpr uint32_t END = 0xFFFFu;                           // delta of a chain that is over: d + END > limit
+    uint32_t slot2 = (p % LINK_RING) * 2u;                      // byte offset of the link slot the walk stands on
+    uint32_t delta = maxlen >= 6 ? lds_u16(link_s + slot2) : END;   // the last five positions of a chunk walk no chain
     uint32_t d = 0;
     int depth = lp.depth;
-    uint32_t scan_end = ring_ld8(S.ring32, p + best);
-    while (__any_sync(FULL, active)) {
+    uint32_t pb = p + (uint32_t)best;                           // filter byte: the one after the best match so far
+    uint32_t scan_end = lds_u8(ring_s + (pb & 0xFFFFu));
+    while (__any_sync(FULL, delta != END)) {
         uint32_t pend0 = 0, pend1 = 0;
-#pragma unroll 1
-        for (int st = 0; st < lp.walk_steps; st++) {
-            if (lp.walk_exit && !__any_sync(FULL, active && pend1 == 0u)) break;
-            if (active && pend1 == 0u) {
-                if (delta == 0u || depth == 0) active = false;
+#pragma unroll
+        for (int st = 0; st < WALK_STEPS; st++) {
+            const uint32_t nd = d + delta;
+            if (pend1 == 0u) {
+                if (nd > limit) delta = END;
                 else {
-                    d += delta;
-                    if (d > limit) active = false;
-                    else {
-                        depth--;
-                        slot -= (int32_t)delta; if (slot < 0) slot += LINK_RING;
-                        const bool pass = ring_ld8(S.ring32, p - d + best) == scan_end;
-                        delta = S.link[slot];
-                        if (pass) { if (pend0) pend1 = d; else pend0 = d; }
-                    }
+                    d = nd;
+                    slot2 -= 2u * delta; if ((int32_t)slot2 < 0) slot2 += 2u * LINK_RING;
+                    const uint32_t b = lds_u8(ring_s + ((pb - d) & 0xFFFFu));
+                    delta = lds_u16(link_s + slot2);
+                    if (--depth == 0) delta = END;
+                    if (b == scan_end) { if (pend0) pend1 = d; else pend0 = d; }
                 }
             }
         }
-        bool done = false;
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const uint32_t cand = r ? pend1 : pend0;
-            if (cand && !done && ring_ld8(S.ring32, p - cand + best) == scan_end) {
-                int l = match_len(S.ring32, p, p - cand, maxlen);
+        // measure: first noted first; the second one only if it still passes the filter
+        while (__any_sync(FULL, pend0 != 0u)) {
+            if (pend0) {
+                const int l = match_len_s(ring_s, p, p - pend0, maxlen);
                 if (l > best) {
-                    best = l; bdist = cand;
-                    if (l >= nice || l >= maxlen) { done = true; active = false; }
-                    else scan_end = ring_ld8(S.ring32, p + best);
+                    best = l; bdist = pend0; pb = p + (uint32_t)best;
+                    if (l >= nice || l >= maxlen) { delta = END; pend1 = 0; }
+                    else {
+                        scan_end = lds_u8(ring_s + (pb & 0xFFFFu));
+                        if (pend1 && lds_u8(ring_s + ((pb - pend1) & 0xFFFFu)) != scan_end) pend1 = 0;
+                    }
                 }
+                pend0 = pend1; pend1 = 0;
             }
         }
     }
@@ -294,14 +305,14 @@ __device__ void search_group(Smem& S, const LevelParams& lp, uint32_t t, uint32_
         if (best < 6 && lp.use_h4) {
             uint32_t d4 = S.c4[t & 1][g * 32u + lane];
             if (d4 != 0u && d4 <= limit && maxlen >= 4) {
-                int l = match_len(S.ring32, p, p - d4, maxlen);
+                int l = match_len_s(ring_s, p, p - d4, maxlen);
                 if (l >= 4 && l > best) { best = l; bdist = d4; }
             }
         }
         if (best < 3 && lp.use_h3) {
             uint32_t d3 = S.c3[t & 1][g * 32u + lane];
             if (d3 != 0u && d3 <= min(limit, (uint32_t)TOO_FAR)) {
-                int l = match_len(S.ring32, p, p - d3, maxlen);
+                int l = match_len_s(ring_s, p, p - d3, maxlen);
                 if (l >= 3) { best = l; bdist = d3; }
             }
         }
@@ -329,19 +340,21 @@ __device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams&
 
 // ---- parse + emission of one tile, by the parser group (warps 0..PARSE_WARPS-1, named barrier 1) -------
 constexpr int PARSE_WARPS = 8;
-constexpr int PARSE_WARP0 = 18;              // warps 18..25
+// Roles by warp.  A warp's scheduler (SMSP) is warp & 3: the three serial inserters and the loader sit together on
+// SMSP 3 with four of the parser warps (which mostly wait at their group barrier), so that the latency-bound
+// inserters get issue slots that eight search warps per scheduler would otherwise take.
+enum { ROLE_INS0 = 0, ROLE_INS1 = 1, ROLE_INS2 = 2, ROLE_LOAD = 3, ROLE_SEARCH = 4, ROLE_PARSE0 = 8 };
+__device__ __forceinline__ int role_of(uint32_t warp)
+{
+    const uint32_t sm = warp & 3u, q = warp >> 2;
+    if (sm == 3u) return q < 4u ? (int)q : ROLE_PARSE0 + (int)(q - 4u);
+    if (sm == 2u && q >= 4u) return ROLE_PARSE0 + 4 + (int)(q - 4u);
+    return ROLE_SEARCH;
+}
 constexpr int PG = PARSE_WARPS * 32;              // threads of the parser group
 constexpr int PPT = (TILE + PG - 1) / PG;         // positions per parser thread
 
 __device__ __forceinline__ void group_sync() { asm volatile("bar.sync 1, %0;" :: "n"(PG) : "memory"); }
-__device__ __forceinline__ bool group_sync_or(bool pred)
-{
-    uint32_t out;
-    asm volatile("{ .reg .pred p, q; setp.ne.u32 p, %1, 0; bar.red.or.pred q, 1, %2, p; selp.u32 %0, 1, 0, q; }"
-                 : "=r"(out) : "r"((uint32_t)pred), "n"(PG) : "memory");
-    return out != 0u;
-}
-
 __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid, uint32_t nthr)
 {
     // histograms of the block that just ended -> global; reset for the next one
@@ -498,9 +511,12 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem& S = *reinterpret_cast<Smem*>(smem_raw);
+    uint32_t sbase;                                  // shared-space address of S, pinned in a register (volatile: not rematerialised)
+    asm volatile("{ .reg .u64 t; cvta.to.shared.u64 t, %1; cvt.u32.u64 %0, t; }" : "=r"(sbase) : "l"(smem_raw));
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     const uint32_t nruns = (nchunks + run - 1) / run;
+    const int role = role_of(warp);
 
     for (;;) {
         __syncthreads();
@@ -541,30 +557,31 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             if (tid == 0) { S.grp_ctr[par ^ 1u] = 0; S.post_ctr[par ^ 1u] = 0; S.ins_done[par ^ 1u] = 0; }   // next iteration's counters
             // roles: three serial inserter warps (raw heads), one loader, eight parser warps; everybody else -- and
             // everybody who is done -- searches
-            if (warp >= 29) {
+            if (role <= ROLE_INS2) {
                 if (do_insert) {
                     long long c0 = clock64();
                     const uint32_t t = (uint32_t)(k + 1);
-                    if (warp == 31) insert_tile<0>(S, t, n_s, lane, 0u, 0u);
-                    else if (warp == 30) insert_tile<1>(S, t, n_s, lane, 0u, 0u);
+                    if (role == ROLE_INS0) insert_tile<0>(S, t, n_s, lane, 0u, 0u);
+                    else if (role == ROLE_INS1) insert_tile<1>(S, t, n_s, lane, 0u, 0u);
                     else insert_tile<2>(S, t, n_s, lane, 0u, 0u);
                     pf[6] += (unsigned long long)(clock64() - c0);
                 }
                 __syncwarp();
                 if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_done[par], 1u); }
-            } else if (warp == 26) {
+            } else if (role == ROLE_LOAD) {
                 load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
                 __syncwarp();
                 if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_done[par], 1u); }
-            } else if (do_parse && warp >= (uint32_t)PARSE_WARP0 && warp < (uint32_t)(PARSE_WARP0 + PARSE_WARPS)) {
+            } else if (do_parse && role >= ROLE_PARSE0) {
                 long long cl0 = clock64();
                 const uint32_t ci = ((uint32_t)(k - 1) * TILE - D) / chunk;              // chunk of the run that tile k-1 belongs to
                 const uint32_t cs = D + ci * chunk, ce = min(cs + chunk, n_s);
                 const uint32_t ncb = ce - cs;
                 parse_emit_tile(S, lp, k - 1, cs, ce, (ncb + BLOCK_SPAN - 1) / BLOCK_SPAN, tokens + (size_t)(c0 + ci) * chunk,
-                                blocks + (size_t)(c0 + ci) * bpc, &chunks[c0 + ci], tid - PARSE_WARP0 * 32u);
+                                blocks + (size_t)(c0 + ci) * bpc, &chunks[c0 + ci], (uint32_t)(role - ROLE_PARSE0) * 32u + lane);
                 pf[6] += (unsigned long long)(clock64() - cl0);
             }
+            const long long ph0 = clock64();
             if (do_search) {
                 const uint32_t ci = ((uint32_t)k * TILE - D) / chunk;
                 const uint32_t ce = min(D + (ci + 1u) * chunk, n_s);                       // end of tile k's chunk
@@ -574,13 +591,17 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     g = __shfl_sync(FULL, g, 0);
                     if (g >= (uint32_t)GROUPS_PER_TILE) break;
                     if ((uint32_t)k * TILE + g * 32u >= ce) continue;
-                    search_group(S, lp, (uint32_t)k, g, ce, lane);
+                    search_group(S, sbase, lp, (uint32_t)k, g, ce, lane);
                 }
             }
             // whoever runs out of work turns the raw heads of tile k+1 into final links, 32 positions at a time, as soon
             // as the inserters are through
+            const long long ph1 = clock64();
+            long long ph2 = ph1;
             if (do_insert) {
-                while (*(volatile uint32_t*)&S.ins_done[par] < 4u) __nanosleep(250);
+                if (lane == 0) while (*(volatile uint32_t*)&S.ins_done[par] < 4u) __nanosleep(400);
+                __syncwarp();
+                ph2 = clock64();
                 __threadfence_block();
                 for (;;) {
                     uint32_t g = 0;
@@ -590,21 +611,26 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     finish_pos(S, (uint32_t)(k + 1), n_s, g * 32u + lane);
                 }
             }
+            const long long ph3 = clock64();
             __syncthreads();
             // the buckets of tile k+2 are parked in slots that the search of tile k was still reading
             if (do_hash) hash_tile(S, (uint32_t)(k + 2), tid);
             __syncthreads();
+            const long long ph4 = clock64();
+            pf[0] += (unsigned long long)(ph1 - ph0); pf[1] += (unsigned long long)(ph2 - ph1);
+            pf[2] += (unsigned long long)(ph3 - ph2); pf[3] += (unsigned long long)(ph4 - ph3);
             pf[7]++;
         }
 
         // ---- run epilogue ----
         if (tid == 0) {
             atomicAdd(&g_lzprof[7], pf[7]);
+            for (int i = 0; i < 4; i++) atomicAdd(&g_lzprof[i], pf[i]);
         }
-        if (tid == 31 * 32) atomicAdd(&g_lzprof[8], pf[6]);
-        if (tid == 30 * 32) atomicAdd(&g_lzprof[9], pf[6]);
-        if (tid == 29 * 32) atomicAdd(&g_lzprof[10], pf[6]);
-        if (tid == 18 * 32) atomicAdd(&g_lzprof[11], pf[6]);
+        if (lane == 0 && role == ROLE_INS0) atomicAdd(&g_lzprof[8], pf[6]);
+        if (lane == 0 && role == ROLE_INS1) atomicAdd(&g_lzprof[9], pf[6]);
+        if (lane == 0 && role == ROLE_INS2) atomicAdd(&g_lzprof[10], pf[6]);
+        if (lane == 0 && role == ROLE_PARSE0) atomicAdd(&g_lzprof[11], pf[6]);
     }
 }
 
