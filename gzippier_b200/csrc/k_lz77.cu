@@ -60,9 +60,7 @@ struct Smem {
     uint32_t masks[TILE / 32];            // token-start bitmap of the tile being parsed
     uint32_t seg_prefix[TILE / 32 + 1];
     uint16_t jump[2][TILE];               // pointer doubling: 2^r-th successor of every position (TILE = leaves the tile)
-    uint32_t grp_ctr[2];                  // dynamic group scheduler of the search phase (alternating per iteration, like the next two)
-    uint32_t post_ctr[2];                 // ... of the finish/hash work that follows it
-    uint32_t ins_done[2];                 // inserter + loader warps that have finished their part of the iteration
+    uint32_t grp_ctr[2];                  // dynamic group scheduler of the search phase (alternating per iteration)
     uint32_t chunk_idx;
     uint32_t entry;                       // next token start (stream position)
     uint32_t ntok;                        // tokens emitted so far in this chunk
@@ -220,27 +218,49 @@ __device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, ui
     }
 }
 
+// Raw head (a 16-bit position) -> delta.  No check against the bytes is needed: sweep_tables keeps every table entry
+// either younger than 32 Ki positions -- then it is a position of this bucket, the most recent one -- or at an age in
+// [32 Ki, 64 Ki), which the range test rejects.
 __device__ __forceinline__ void finish_pos(Smem& S, uint32_t t, uint32_t n_s, uint32_t o)
 {
     const uint32_t base = t * TILE, p = base + o;
     if (p >= n_s) return;
-    const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);
     uint32_t slot = base % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
-    {
-        const uint32_t d = (p - (uint32_t)S.link[slot]) & 0xFFFFu;
-        const bool ok = d != 0u && d <= 32767u && d <= p;
-        const uint32_t c = ok ? p - d : p;
-        S.link[slot] = (uint16_t)((ok && bucket_of<0>(ring_ld32(S.ring32, c), ring_ld32(S.ring32, c + 4u)) == bucket_of<0>(v, v2)) ? d : 0xFFFFu);
-    }
-    {
-        const uint32_t d = (p - (uint32_t)S.c3[t & 1][o]) & 0xFFFFu;
-        const bool ok = d != 0u && d <= (uint32_t)TOO_FAR && d <= p;
-        S.c3[t & 1][o] = (uint16_t)((ok && hash3(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash3(v)) ? d : 0u);
-    }
-    {
-        const uint32_t d = (p - (uint32_t)S.c4[t & 1][o]) & 0xFFFFu;
-        const bool ok = d != 0u && d <= 32767u && d <= p;
-        S.c4[t & 1][o] = (uint16_t)((ok && hash4(ring_ld32(S.ring32, p - (ok ? d : 0u))) == hash4(v)) ? d : 0u);
+    const uint32_t d6 = (p - (uint32_t)S.link[slot]) & 0xFFFFu;
+    const uint32_t d3 = (p - (uint32_t)S.c3[t & 1][o]) & 0xFFFFu;
+    const uint32_t d4 = (p - (uint32_t)S.c4[t & 1][o]) & 0xFFFFu;
+    S.link[slot] = (uint16_t)(d6 - 1u < 32767u ? d6 : 0xFFFFu);
+    S.c3[t & 1][o] = (uint16_t)(d3 - 1u < (uint32_t)TOO_FAR ? d3 : 0u);
+    S.c4[t & 1][o] = (uint16_t)(d4 - 1u < 32767u ? d4 : 0u);
+}
+__device__ __forceinline__ void finish_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t tid)
+{
+#pragma unroll
+    for (int j = 0; j < TILE / LZ_THREADS; j++) finish_pos(S, t, n_s, tid + (uint32_t)j * LZ_THREADS);
+}
+
+// Ageing of the 16-bit table entries.  Before tile t is inserted, one eighth of every table is swept: an entry older
+// than 32767 positions is replaced by the position exactly 32 Ki back.  Every entry is visited once per 16 Ki positions,
+// so no entry ever reaches the age of 64 Ki at which its 16 bits would alias a recent position; the tables start a
+// run filled with 0x8000, which is that marker for position 0.
+constexpr uint32_t TABLE_FILL = 0x80008000u;
+__device__ __forceinline__ uint32_t sweep_pair(uint32_t w, uint32_t p16)
+{
+    const uint32_t mark = p16 ^ 0x8000u;
+    uint32_t lo = w & 0xFFFFu, hi = w >> 16;
+    if (((p16 - lo) & 0xFFFFu) > 32767u) lo = mark;
+    if (((p16 - hi) & 0xFFFFu) > 32767u) hi = mark;
+    return lo | (hi << 16);
+}
+__device__ __forceinline__ void sweep_tables(Smem& S, uint32_t t, uint32_t tid)
+{
+    const uint32_t p16 = (t * TILE) & 0xFFFFu, slice = t & 7u;
+    static_assert((1u << HBITS) / 2 / 8 == LZ_THREADS && (1u << H3BITS) / 2 / 8 == 256 && (1u << H4BITS) / 2 / 8 == 256, "sweep slices");
+    uint32_t* h6 = reinterpret_cast<uint32_t*>(S.head) + slice * LZ_THREADS + tid;
+    *h6 = sweep_pair(*h6, p16);
+    if (tid < 512u) {
+        uint32_t* hx = reinterpret_cast<uint32_t*>(tid < 256u ? S.head3 : S.head4) + slice * 256u + (tid & 255u);
+        *hx = sweep_pair(*hx, p16);
     }
 }
 
@@ -536,12 +556,12 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
 
         unsigned long long pf[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         // ---- per-run reset ----
-        for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = 0;
-        for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = 0;
-        for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = 0;
+        for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = TABLE_FILL;
+        for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = TABLE_FILL;
+        for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = TABLE_FILL;
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
-        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[1] = 0; S.post_ctr[1] = 0; S.ins_done[1] = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
+        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[1] = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
         for (uint32_t t = 0; t < 3; t++) load_tile(S, sp, n_s, t, tid, LZ_THREADS);
         __syncthreads();
         hash_tile(S, 0u, tid);
@@ -554,7 +574,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             const bool do_parse = k - 1 >= (int)first_ctile;                      // k - 1 < ntiles by the loop bound
             const bool do_search = k >= (int)first_ctile && k < (int)ntiles;
             const uint32_t par = (uint32_t)k & 1u;
-            if (tid == 0) { S.grp_ctr[par ^ 1u] = 0; S.post_ctr[par ^ 1u] = 0; S.ins_done[par ^ 1u] = 0; }   // next iteration's counters
+            if (tid == 0) S.grp_ctr[par ^ 1u] = 0;                                // next iteration's counter
             // roles: three serial inserter warps (raw heads), one loader, eight parser warps; everybody else -- and
             // everybody who is done -- searches
             if (role <= ROLE_INS2) {
@@ -566,12 +586,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     else insert_tile<2>(S, t, n_s, lane, 0u, 0u);
                     pf[6] += (unsigned long long)(clock64() - c0);
                 }
-                __syncwarp();
-                if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_done[par], 1u); }
             } else if (role == ROLE_LOAD) {
                 load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
-                __syncwarp();
-                if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_done[par], 1u); }
             } else if (do_parse && role >= ROLE_PARSE0) {
                 long long cl0 = clock64();
                 const uint32_t ci = ((uint32_t)(k - 1) * TILE - D) / chunk;              // chunk of the run that tile k-1 belongs to
@@ -594,27 +610,13 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     search_group(S, sbase, lp, (uint32_t)k, g, ce, lane);
                 }
             }
-            // whoever runs out of work turns the raw heads of tile k+1 into final links, 32 positions at a time, as soon
-            // as the inserters are through
-            const long long ph1 = clock64();
-            long long ph2 = ph1;
-            if (do_insert) {
-                if (lane == 0) while (*(volatile uint32_t*)&S.ins_done[par] < 4u) __nanosleep(400);
-                __syncwarp();
-                ph2 = clock64();
-                __threadfence_block();
-                for (;;) {
-                    uint32_t g = 0;
-                    if (lane == 0) g = atomicAdd(&S.post_ctr[par], 1u);
-                    g = __shfl_sync(FULL, g, 0);
-                    if (g >= (uint32_t)GROUPS_PER_TILE) break;
-                    finish_pos(S, (uint32_t)(k + 1), n_s, g * 32u + lane);
-                }
-            }
+            const long long ph1 = clock64(), ph2 = ph1;
             const long long ph3 = clock64();
             __syncthreads();
-            // the buckets of tile k+2 are parked in slots that the search of tile k was still reading
-            if (do_hash) hash_tile(S, (uint32_t)(k + 2), tid);
+            // between the barriers the tables are at rest: raw heads of tile k+1 -> links, buckets of tile k+2 parked (in
+            // slots that the search of tile k was still reading), one slice of the tables aged
+            if (do_insert) finish_tile(S, (uint32_t)(k + 1), n_s, tid);
+            if (do_hash) { hash_tile(S, (uint32_t)(k + 2), tid); sweep_tables(S, (uint32_t)(k + 2), tid); }
             __syncthreads();
             const long long ph4 = clock64();
             pf[0] += (unsigned long long)(ph1 - ph0); pf[1] += (unsigned long long)(ph2 - ph1);
