@@ -232,6 +232,7 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     const uint64_t nchunks64 = (n + chunk - 1) / chunk;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     LevelParams lp = level_params(level);
+    lp.parse_warps = getenv("GZB_PW") ? atoi(getenv("GZB_PW")) : (level <= 3 ? 16 : 8);
     ctx->n_sub_timed = 0;
 
     CU(ctx, cudaMemsetAsync(ctx->d_cursor, 0, sizeof(Cursor), st));

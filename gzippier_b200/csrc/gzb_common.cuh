@@ -35,6 +35,7 @@ constexpr int      HDR_BYTES   = 608;             // worst case 14 + 57 + 316*14
 // (lib/zlib/deflate.c:134-146); depth replaces max_chain (DESIGN.md "Level semantics").
 struct LevelParams {
     int depth, nice, max_lazy, lazy_parse, use_h3, use_h4;
+    int parse_warps;                         // 8 or 16: size of k_lz77's parser group (no effect on the result)
 };
 
 // One deflate block.  Written by k_lz77 (histograms, token range, input range),

@@ -87,6 +87,7 @@ __device__ __forceinline__ uint32_t ring_ld8(const uint32_t* ring32, uint32_t po
 // arithmetic, and the compiler has nothing to re-derive inside the loop.
 __device__ __forceinline__ uint32_t lds_u8(uint32_t a)  { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t lds_u16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "h"((uint16_t)v) : "memory"); }
 template <int OFF>
 __device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFF)); return v; }
 
@@ -139,9 +140,9 @@ __device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n
 //   insert_tile  (one warp per table)   old = head[h]; head[h] = p; store `old` raw.  Lanes of a step that share
 //                                       a bucket are detected by write-then-read-back and ordered with ballots
 //                                       (MATCH.ANY would tell the same, at ~500 cycles per step)
-//   finish_tile  (all threads, after)   raw head -> delta, rejecting stale/aliased heads by re-hashing the bytes
-//                                       at the candidate, so a chain is exactly "all earlier positions of the
-//                                       bucket, most recent first"
+//   finish_tile  (all threads, after)   raw head -> delta; sweep_tables ages the entries, so a range test is all it
+//                                       takes for a chain to be exactly "all earlier positions of the bucket
+//                                       within 32 Ki, most recent first"
 // KIND 0: 6-byte buckets -> S.link (chains); KIND 1 / 2: 3-byte / 4-byte buckets -> S.c3 (within TOO_FAR) / S.c4.
 template <int KIND>
 __device__ __forceinline__ uint32_t bucket_of(uint32_t v, uint32_t v2)
@@ -163,57 +164,56 @@ __device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
     for (int j = 0; j < TILE / LZ_THREADS; j++) hash_pos(S, t, tid + (uint32_t)j * LZ_THREADS);
 }
 
-// cls / cmask: only the buckets with (bucket & cmask) == cls are inserted (0, 0 = all).
+// One step = 32 consecutive positions, lane = position.  The loop is written on shared-space addresses and kept as
+// short as it goes: a step costs its instruction count times the issue interval of a warp that shares its scheduler
+// with seven busy ones.
 template <int KIND>
-__device__ void insert_tile(Smem& S, uint32_t t, uint32_t n_s, uint32_t lane, uint32_t cls, uint32_t cmask)
+__device__ void insert_tile(Smem& S, uint32_t sbase, uint32_t t, uint32_t n_s, uint32_t lane)
 {
-    const uint32_t base = t * TILE;
-    uint16_t* table = KIND == 0 ? S.head : KIND == 1 ? S.head3 : S.head4;
-    uint16_t* cx = KIND == 1 ? S.c3[t & 1] : S.c4[t & 1];
-    uint32_t slot = base % LINK_RING + lane;
+    (void)S;
+    const uint32_t base = t * TILE;                                           // < n_s
+    const uint32_t nsteps = min((uint32_t)GROUPS_PER_TILE, (n_s - base + 31u) / 32u);   // nothing past the end is ever searched
+    const uint32_t table_s = sbase + (uint32_t)(KIND == 0 ? offsetof(Smem, head) : KIND == 1 ? offsetof(Smem, head3) : offsetof(Smem, head4));
+    // where the buckets are parked and the raw heads go; a tile's link slots are contiguous (LINK_RING % TILE == 0)
+    static_assert(LINK_RING % TILE == 0, "a tile's link slots must not wrap");
+    uint32_t dst = sbase + (KIND == 0 ? (uint32_t)offsetof(Smem, link) + 2u * (base % LINK_RING + lane)
+                                      : (uint32_t)(KIND == 1 ? offsetof(Smem, c3) : offsetof(Smem, c4)) + 2u * ((t & 1u) * TILE + lane));
+    uint32_t p16 = (base + lane) & 0xFFFFu;                                   // + 32 per step: no wrap inside a tile
     const uint32_t lt_mask = (1u << lane) - 1u;
-    uint32_t hn = KIND == 0 ? (uint32_t)S.link[slot] : (uint32_t)cx[lane];
-    for (uint32_t i = 0; i < GROUPS_PER_TILE; i++) {
-        if (base + i * 32u >= n_s) break;                       // nothing past the end is ever searched
-        const uint32_t p16 = (base + i * 32u + lane) & 0xFFFFu;
-        uint32_t h = hn;
-        const uint32_t slot_now = slot;
-        slot += 32u; if (slot >= LINK_RING) slot -= LINK_RING;
-        if (i + 1u < GROUPS_PER_TILE) hn = KIND == 0 ? (uint32_t)S.link[slot] : (uint32_t)cx[(i + 1u) * 32u + lane];   // next step's buckets
-        const bool act = (h & cmask) == cls;
-        if (!act) h = 0xFFFFFFFFu;                              // never equal to a real bucket
-        uint32_t raw = act ? (uint32_t)table[h] : 0u;
+    uint32_t ta = table_s + 2u * lds_u16(dst);
+    for (uint32_t i = 0; i < nsteps; i++, dst += 64u, p16 += 32u) {
+        const uint32_t hn = lds_u16(dst + 64u);                              // next step's bucket (garbage after the last step, unused)
+        uint32_t raw = lds_u16(ta);
         // Write, read back: a lane that does not find its own position shares its bucket with another lane of the step.
         // The losers then write once more: a bucket shared by exactly TWO lanes -- the usual case -- is settled by these
         // two exchanges (each lane has read the other's position); only buckets with three or more lanes of the step
         // need MATCH.ANY (~450 cycles).
         __syncwarp();
-        if (act) table[h] = (uint16_t)p16;
+        sts_u16(ta, p16);
         __syncwarp();
-        const uint32_t r1 = act ? (uint32_t)table[h] : p16;
+        const uint32_t r1 = lds_u16(ta);
         const bool lost = r1 != p16;
-        if (__ballot_sync(FULL, lost)) {                         // uniform
+        if (__any_sync(FULL, lost)) {                            // uniform
             __syncwarp();
-            if (lost) table[h] = (uint16_t)p16;
+            if (lost) sts_u16(ta, p16);
             __syncwarp();
-            const uint32_t r2 = act ? (uint32_t)table[h] : p16;
-            if (__ballot_sync(FULL, lost && r2 != p16) == 0u) {
+            const uint32_t r2 = lds_u16(ta);
+            if (!__any_sync(FULL, lost && r2 != p16)) {
                 const bool paired = lost || r2 != p16;
                 const uint32_t partner = lost ? r1 : r2;
-                const bool partner_lower = ((p16 - partner) & 0xFFFFu) < 32u;
+                const bool partner_lower = partner < p16;                    // same tile: no wrap
                 if (paired && partner_lower) raw = partner;                  // the other lane of the bucket precedes me
                 __syncwarp();
-                if (paired && partner_lower && !lost) table[h] = (uint16_t)p16;   // the later position owns the bucket
+                if (paired && partner_lower && !lost) sts_u16(ta, p16);      // the later position owns the bucket
             } else {
-                const uint32_t same = __match_any_sync(FULL, h);
-                if (act) {
-                    const uint32_t lower = same & lt_mask;
-                    if (lower) raw = (p16 - (lane - (uint32_t)(31 - __clz(lower)))) & 0xFFFFu;   // the nearest lower lane of the bucket
-                    if ((same >> lane) == 1u && lower) table[h] = (uint16_t)p16;               // the last position of the step owns the bucket
-                }
+                const uint32_t same = __match_any_sync(FULL, ta);
+                const uint32_t lower = same & lt_mask;
+                if (lower) raw = p16 - (lane - (uint32_t)(31 - __clz(lower)));   // the nearest lower lane of the bucket
+                if ((same >> lane) == 1u && lower) sts_u16(ta, p16);             // the last position of the step owns the bucket
             }
         }
-        if (act) { if (KIND == 0) S.link[slot_now] = (uint16_t)raw; else cx[i * 32u + lane] = (uint16_t)raw; }
+        sts_u16(dst, raw);
+        ta = table_s + 2u * hn;
         __syncwarp();
     }
 }
@@ -359,22 +359,22 @@ __device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams&
 }
 
 // ---- parse + emission of one tile, by the parser group (warps 0..PARSE_WARPS-1, named barrier 1) -------
-constexpr int PARSE_WARPS = 8;
+// PARSE_WARPS (8 or 16) is a template parameter of the kernel: the cheap searches of the low levels finish long before an
+// 8-warp parser does, the deep ones want the warps for searching.
 // Roles by warp.  A warp's scheduler (SMSP) is warp & 3: the three serial inserters and the loader sit together on
 // SMSP 3 with four of the parser warps (which mostly wait at their group barrier), so that the latency-bound
 // inserters get issue slots that eight search warps per scheduler would otherwise take.
 enum { ROLE_INS0 = 0, ROLE_INS1 = 1, ROLE_INS2 = 2, ROLE_LOAD = 3, ROLE_SEARCH = 4, ROLE_PARSE0 = 8 };
+template <int PARSE_WARPS>
 __device__ __forceinline__ int role_of(uint32_t warp)
 {
     const uint32_t sm = warp & 3u, q = warp >> 2;
     if (sm == 3u) return q < 4u ? (int)q : ROLE_PARSE0 + (int)(q - 4u);
-    if (sm == 2u && q >= 4u) return ROLE_PARSE0 + 4 + (int)(q - 4u);
-    return ROLE_SEARCH;
+    if (PARSE_WARPS == 8) return (sm == 2u && q >= 4u) ? ROLE_PARSE0 + 4 + (int)(q - 4u) : ROLE_SEARCH;
+    return q >= 4u ? ROLE_PARSE0 + 4 + (int)(sm * 4u + q - 4u) : ROLE_SEARCH;
 }
-constexpr int PG = PARSE_WARPS * 32;              // threads of the parser group
-constexpr int PPT = (TILE + PG - 1) / PG;         // positions per parser thread
 
-__device__ __forceinline__ void group_sync() { asm volatile("bar.sync 1, %0;" :: "n"(PG) : "memory"); }
+template <int PG> __device__ __forceinline__ void group_sync_n() { asm volatile("bar.sync 1, %0;" :: "n"(PG) : "memory"); }
 __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid, uint32_t nthr)
 {
     // histograms of the block that just ended -> global; reset for the next one
@@ -395,9 +395,13 @@ __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in
 // Then every marked position emits its token; index = prefix popcount of the marks.
 // D / n_s: stream positions where the tile's chunk starts / ends.  The last tile of a chunk also closes the chunk's
 // last block and its record, and resets the per-chunk counters for the next chunk of the run.
+template <int PARSE_WARPS>
 __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t D, uint32_t n_s, uint32_t nblocks,
                                 uint32_t* __restrict__ tok, BlockRec* __restrict__ brecs, ChunkRec* __restrict__ crec, uint32_t gtid)
 {
+    constexpr int PG = PARSE_WARPS * 32;              // threads of the parser group
+    constexpr int PPT = (TILE + PG - 1) / PG;         // positions per parser thread
+    auto group_sync = [] { group_sync_n<PG>(); };
     const uint32_t lane = gtid & 31u, warp = gtid >> 5;
     const bool last = ((uint32_t)(k + 1) * TILE >= n_s);
     const int base = k * TILE - 1;                        // decidable positions: [base, hi) (lazy needs mlen[p+1])
@@ -416,15 +420,22 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
     constexpr int NWIN = TILE / 32, WPW = NWIN / PARSE_WARPS;
     uint16_t* wexit = S.jump[0];                          // [o]: where the parse entering at o leaves o's window
     uint16_t* went = S.jump[1];                           // [w]: entry position of window w, TILE = not entered
-    uint32_t jrel[WPW];                                   // next(o) relative to its window, 32 = leaves it
+    // per position o = gtid + i * PG: its match token (0 = literal) | next(o) relative to its window (32 = leaves it) << 24
+    uint32_t pk[WPW];
     // 1.
 #pragma unroll
     for (int i = 0; i < WPW; i++) {
         const int w = (int)warp + i * PARSE_WARPS, o = w * 32 + (int)lane;
         int nx = TILE + 512;
-        if (o < lim) { bool lit; uint32_t dd; nx = o + (int)parse_step(S, lp, (uint32_t)(base + o), n_s, lit, dd); }
+        uint32_t tokv = 0;
+        if (o < lim) {
+            bool lit; uint32_t dd;
+            const uint32_t step = parse_step(S, lp, (uint32_t)(base + o), n_s, lit, dd);
+            nx = o + (int)step;
+            if (!lit) tokv = tok_match(step, dd);
+        }
         uint32_t j = (nx < lim && nx - w * 32 < 32) ? (uint32_t)(nx - w * 32) : 32u;
-        jrel[i] = j;
+        pk[i] = tokv | (j << 24);
         int x = nx;
 #pragma unroll
         for (int r = 0; r < 5; r++) {
@@ -454,7 +465,7 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
         uint32_t m = 0;
         if (e < (uint32_t)TILE) {                           // uniform per warp
             m = 1u << (e & 31u);
-            uint32_t j = jrel[i];
+            uint32_t j = (pk[i] >> 24) & 63u;
 #pragma unroll
             for (int r = 0; r < 5; r++) {
                 m |= __reduce_or_sync(FULL, (((m >> lane) & 1u) && j < 32u) ? 1u << j : 0u);
@@ -479,19 +490,15 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
 #pragma unroll
         for (int r = 0; r < PPT; r++) {
             const uint32_t o = gtid + (uint32_t)r * PG;
-            if (o >= (uint32_t)TILE) continue;
             const uint32_t seg = o >> 5, bit = o & 31u;
             const uint32_t mk = S.masks[seg];
             if ((mk >> bit) & 1u) {
                 const uint32_t idx = ntok0 + S.seg_prefix[seg] + (uint32_t)__popc(mk & ((1u << bit) - 1u));
-                const uint32_t p = (uint32_t)(base + (int)o);
-                bool lit; uint32_t dist; const uint32_t step = parse_step(S, lp, p, n_s, lit, dist);
-                uint32_t tv;
-                if (lit) { tv = ring_ld8(S.ring32, p); atomicAdd(&S.lfreq[tv], 1u); }
+                uint32_t tv = pk[r] & 0x80FFFFFFu;
+                if (tv == 0u) { tv = ring_ld8(S.ring32, (uint32_t)(base + (int)o)); atomicAdd(&S.lfreq[tv], 1u); }
                 else {
-                    tv = tok_match(step, dist);
-                    atomicAdd(&S.lfreq[257u + len_code(step)], 1u);
-                    atomicAdd(&S.dfreq[dist_code(dist)], 1u);
+                    atomicAdd(&S.lfreq[257u + len_code(((tv >> 16) & 0xFFu) + 3u)], 1u);
+                    atomicAdd(&S.dfreq[dist_code((tv & 0xFFFFu) + 1u)], 1u);
                 }
                 tok[idx] = tv;
             }
@@ -524,6 +531,7 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
 // One CTA takes a RUN of `run` consecutive chunks and treats them as one stream: the hash tables and chains it has
 // at the end of a chunk are the next chunk's dictionary, so only the first chunk of a run pays for inserting its
 // 32 KiB dictionary (deflateSetDictionary) -- the parse, the tokens and the blocks stay per chunk.
+template <int PARSE_WARPS>
 __global__ void __launch_bounds__(LZ_THREADS, 1)
 k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks, uint32_t run,
        uint32_t* __restrict__ tokens, BlockRec* __restrict__ blocks, ChunkRec* __restrict__ chunks, LevelParams lp,
@@ -536,7 +544,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     const uint32_t nruns = (nchunks + run - 1) / run;
-    const int role = role_of(warp);
+    const int role = role_of<PARSE_WARPS>(warp);
 
     for (;;) {
         __syncthreads();
@@ -581,9 +589,9 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 if (do_insert) {
                     long long c0 = clock64();
                     const uint32_t t = (uint32_t)(k + 1);
-                    if (role == ROLE_INS0) insert_tile<0>(S, t, n_s, lane, 0u, 0u);
-                    else if (role == ROLE_INS1) insert_tile<1>(S, t, n_s, lane, 0u, 0u);
-                    else insert_tile<2>(S, t, n_s, lane, 0u, 0u);
+                    if (role == ROLE_INS0) insert_tile<0>(S, sbase, t, n_s, lane);
+                    else if (role == ROLE_INS1) insert_tile<1>(S, sbase, t, n_s, lane);
+                    else insert_tile<2>(S, sbase, t, n_s, lane);
                     pf[6] += (unsigned long long)(clock64() - c0);
                 }
             } else if (role == ROLE_LOAD) {
@@ -593,7 +601,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 const uint32_t ci = ((uint32_t)(k - 1) * TILE - D) / chunk;              // chunk of the run that tile k-1 belongs to
                 const uint32_t cs = D + ci * chunk, ce = min(cs + chunk, n_s);
                 const uint32_t ncb = ce - cs;
-                parse_emit_tile(S, lp, k - 1, cs, ce, (ncb + BLOCK_SPAN - 1) / BLOCK_SPAN, tokens + (size_t)(c0 + ci) * chunk,
+                parse_emit_tile<PARSE_WARPS>(S, lp, k - 1, cs, ce, (ncb + BLOCK_SPAN - 1) / BLOCK_SPAN, tokens + (size_t)(c0 + ci) * chunk,
                                 blocks + (size_t)(c0 + ci) * bpc, &chunks[c0 + ci], (uint32_t)(role - ROLE_PARSE0) * 32u + lane);
                 pf[6] += (unsigned long long)(clock64() - cl0);
             }
@@ -647,7 +655,9 @@ cudaError_t lz77_read_prof(unsigned long long* out16, int reset)
 
 cudaError_t lz77_configure()
 {
-    return cudaFuncSetAttribute(k_lz77, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    cudaError_t e = cudaFuncSetAttribute(k_lz77<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_lz77<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
 }
 
 void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
@@ -660,7 +670,8 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
     if (dict) { run = nchunks / (4u * (uint32_t)n_sm); run = run < 1u ? 1u : run > 4u ? 4u : run; }
     const uint32_t nruns = (nchunks + run - 1) / run;
     const uint32_t grid = nruns < (uint32_t)n_sm ? nruns : (uint32_t)n_sm;
-    k_lz77<<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
+    if (lp.parse_warps == 16) k_lz77<16><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
+    else k_lz77<8><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
 }
 
 }  // namespace gzb
