@@ -61,6 +61,10 @@ struct Smem {
     uint32_t seg_prefix[TILE / 32 + 1];
     uint16_t jump[2][TILE];               // pointer doubling: 2^r-th successor of every position (TILE = leaves the tile)
     uint32_t grp_ctr[2];                  // dynamic group scheduler of the search phase (alternating per iteration)
+    uint32_t gctr[3];                     // flowing pipeline: group scheduler of tile t at [t % 3]
+    uint32_t ins_total;                   // ... tiles inserted, summed over the three inserter warps
+    uint32_t parsed;                      // ... tiles of the run parsed
+    uint32_t b1_done;                     // ... k + 2 once the search barrier of iteration k has completed
     uint32_t chunk_idx;
     uint32_t entry;                       // next token start (stream position)
     uint32_t ntok;                        // tokens emitted so far in this chunk
@@ -158,6 +162,10 @@ __device__ __forceinline__ void hash_pos(Smem& S, uint32_t t, uint32_t o)
     uint32_t slot = (t * TILE) % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
     S.link[slot] = (uint16_t)bucket_of<0>(v, v2); S.c3[t & 1][o] = (uint16_t)bucket_of<1>(v, v2); S.c4[t & 1][o] = (uint16_t)bucket_of<2>(v, v2);
 }
+__device__ void hash_tile_n(Smem& S, uint32_t t, uint32_t idx, uint32_t nthr)
+{
+    for (uint32_t o = idx; o < (uint32_t)TILE; o += nthr) hash_pos(S, t, o);
+}
 __device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
 {
 #pragma unroll
@@ -167,7 +175,18 @@ __device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
 // One step = 32 consecutive positions, lane = position.  The loop is written on shared-space addresses and kept as
 // short as it goes: a step costs its instruction count times the issue interval of a warp that shares its scheduler
 // with seven busy ones.
+// raw head (16-bit position) of position p16 -> what the search reads: see finish_pos
 template <int KIND>
+__device__ __forceinline__ uint32_t to_delta(uint32_t p16, uint32_t raw)
+{
+    const uint32_t d = (p16 - raw) & 0xFFFFu;
+    if (KIND == 0) return d - 1u < 32767u ? d : 0xFFFFu;
+    return d - 1u < (KIND == 1 ? (uint32_t)TOO_FAR : 32767u) ? d : 0u;
+}
+
+// DIRECT: store the final delta instead of the raw head (no finish pass: the flowing pipeline needs the links of a tile
+// final as soon as its inserters are through).
+template <int KIND, bool DIRECT>
 __device__ void insert_tile(Smem& S, uint32_t sbase, uint32_t t, uint32_t n_s, uint32_t lane)
 {
     (void)S;
@@ -212,7 +231,7 @@ __device__ void insert_tile(Smem& S, uint32_t sbase, uint32_t t, uint32_t n_s, u
                 if ((same >> lane) == 1u && lower) sts_u16(ta, p16);             // the last position of the step owns the bucket
             }
         }
-        sts_u16(dst, raw);
+        sts_u16(dst, DIRECT ? to_delta<KIND>(p16, raw) : raw);
         ta = table_s + 2u * hn;
         __syncwarp();
     }
@@ -251,6 +270,16 @@ __device__ __forceinline__ uint32_t sweep_pair(uint32_t w, uint32_t p16)
     if (((p16 - lo) & 0xFFFFu) > 32767u) lo = mark;
     if (((p16 - hi) & 0xFFFFu) > 32767u) hi = mark;
     return lo | (hi << 16);
+}
+__device__ __forceinline__ void sweep_tables_n(Smem& S, uint32_t t, uint32_t idx, uint32_t nthr)
+{
+    const uint32_t p16 = (t * TILE) & 0xFFFFu, slice = t & 7u;
+    uint32_t* h6 = reinterpret_cast<uint32_t*>(S.head) + slice * LZ_THREADS;
+    for (uint32_t i = idx; i < (uint32_t)LZ_THREADS; i += nthr) h6[i] = sweep_pair(h6[i], p16);
+    for (uint32_t i = idx; i < 512u; i += nthr) {
+        uint32_t* hx = reinterpret_cast<uint32_t*>(i < 256u ? S.head3 : S.head4) + slice * 256u + (i & 255u);
+        *hx = sweep_pair(*hx, p16);
+    }
 }
 __device__ __forceinline__ void sweep_tables(Smem& S, uint32_t t, uint32_t tid)
 {
@@ -528,10 +557,31 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
     }
 }
 
+__device__ __forceinline__ void bar_sync_n(uint32_t id, uint32_t n) { asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive_n(uint32_t id, uint32_t n) { asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void wait_ge(const uint32_t* flag, uint32_t v, uint32_t lane)
+{
+    if (lane == 0) while (*(volatile const uint32_t*)flag < v) __nanosleep(100);
+    __syncwarp();
+    __threadfence_block();
+}
+// the groups of tile k, handed out dynamically
+__device__ __forceinline__ void search_tile(Smem& S, uint32_t sbase, const LevelParams& lp, uint32_t k, uint32_t ce, uint32_t* ctr, uint32_t lane)
+{
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(ctr, 1u);
+        g = __shfl_sync(FULL, g, 0);
+        if (g >= (uint32_t)GROUPS_PER_TILE) break;
+        if (k * TILE + g * 32u >= ce) continue;
+        search_group(S, sbase, lp, k, g, ce, lane);
+    }
+}
+
 // One CTA takes a RUN of `run` consecutive chunks and treats them as one stream: the hash tables and chains it has
 // at the end of a chunk are the next chunk's dictionary, so only the first chunk of a run pays for inserting its
 // 32 KiB dictionary (deflateSetDictionary) -- the parse, the tokens and the blocks stay per chunk.
-template <int PARSE_WARPS>
+template <int PARSE_WARPS, bool FLOW>
 __global__ void __launch_bounds__(LZ_THREADS, 1)
 k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks, uint32_t run,
        uint32_t* __restrict__ tokens, BlockRec* __restrict__ blocks, ChunkRec* __restrict__ chunks, LevelParams lp,
@@ -569,13 +619,78 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = TABLE_FILL;
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
-        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[1] = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
+        if (tid == 0) { S.entry = D; S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0; S.grp_ctr[1] = 0; S.gctr[0] = 0; S.gctr[1] = 0; S.gctr[2] = 0; S.ins_total = 0; S.parsed = 0; S.b1_done = 0; S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu; }
         for (uint32_t t = 0; t < 3; t++) load_tile(S, sp, n_s, t, tid, LZ_THREADS);
         __syncthreads();
         hash_tile(S, 0u, tid);
         __syncthreads();
 
         // ---- pipeline: iteration k inserts tile k+1, searches tile k and parses + emits tile k-1, all at once ----
+        if constexpr (FLOW) {
+            // Flowing variant.  The role warps (3 inserters, loader, parsers) run the iterations in step, as below; the pure
+            // search warps never wait at a barrier: they only ARRIVE at the search barrier of iteration k (named barrier
+            // 2 + (k & 1)) when they are through with tile k and go straight on to tile k+1, whose links are final as soon
+            // as its inserters are done (DIRECT).  What they must wait for is told by three counters: ins_total (tile
+            // inserted), parsed (the tile whose mlen/mdist slots they are about to rewrite has been parsed) and b1_done (the
+            // previous use of the barrier they are about to arrive at is over).  The barrier section -- parking the buckets
+            // of tile k+2, ageing the tables -- is the role warps' business (named barrier 4).
+            constexpr uint32_t NRT = (4u + (uint32_t)PARSE_WARPS) * 32u;
+            const uint32_t rtid = (uint32_t)(role < 4 ? role : 4 + (role - ROLE_PARSE0)) * 32u + lane;
+            for (int k = -1; k <= (int)ntiles; k++) {
+                const bool do_insert = k + 1 < (int)ntiles;
+                const bool do_hash = k + 2 < (int)ntiles;
+                const bool do_parse = k - 1 >= (int)first_ctile;
+                const bool do_search = k >= (int)first_ctile && k < (int)ntiles;
+                const uint32_t b1 = 2u + ((uint32_t)k & 1u);
+                uint32_t ce = 0;
+                if (do_search) { const uint32_t ci = ((uint32_t)k * TILE - D) / chunk; ce = min(D + (ci + 1u) * chunk, n_s); }
+                if (role == ROLE_SEARCH) {
+                    wait_ge(&S.b1_done, (uint32_t)max(k, 0), lane);
+                    if (do_search) {
+                        wait_ge(&S.ins_total, 3u * (uint32_t)(k + 1), lane);
+                        if (k - 2 >= (int)first_ctile) wait_ge(&S.parsed, (uint32_t)(k - 1 - (int)first_ctile), lane);
+                        const long long ph0 = clock64();
+                        search_tile(S, sbase, lp, (uint32_t)k, ce, &S.gctr[(uint32_t)k % 3u], lane);
+                        pf[0] += (unsigned long long)(clock64() - ph0);
+                    }
+                    __threadfence_block();
+                    bar_arrive_n(b1, LZ_THREADS);
+                } else {
+                    if (role <= ROLE_INS2) {
+                        if (do_insert) {
+                            long long c0 = clock64();
+                            const uint32_t t = (uint32_t)(k + 1);
+                            if (role == ROLE_INS0) insert_tile<0, true>(S, sbase, t, n_s, lane);
+                            else if (role == ROLE_INS1) insert_tile<1, true>(S, sbase, t, n_s, lane);
+                            else insert_tile<2, true>(S, sbase, t, n_s, lane);
+                            pf[6] += (unsigned long long)(clock64() - c0);
+                            __syncwarp();
+                            if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_total, 1u); }
+                        }
+                    } else if (role == ROLE_LOAD) {
+                        load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);
+                    } else if (do_parse) {
+                        long long cl0 = clock64();
+                        const uint32_t ci = ((uint32_t)(k - 1) * TILE - D) / chunk;
+                        const uint32_t cs = D + ci * chunk, cend = min(cs + chunk, n_s);
+                        const uint32_t ncb = cend - cs;
+                        parse_emit_tile<PARSE_WARPS>(S, lp, k - 1, cs, cend, (ncb + BLOCK_SPAN - 1) / BLOCK_SPAN, tokens + (size_t)(c0 + ci) * chunk,
+                                        blocks + (size_t)(c0 + ci) * bpc, &chunks[c0 + ci], (uint32_t)(role - ROLE_PARSE0) * 32u + lane);
+                        pf[6] += (unsigned long long)(clock64() - cl0);
+                        if (role == ROLE_PARSE0 && lane == 0) { __threadfence_block(); *(volatile uint32_t*)&S.parsed = (uint32_t)(k - (int)first_ctile); }
+                    }
+                    // lend a hand with tile k -- at the deep levels, where the search is several times longer than the roles; at
+                    // the others a group taken now would only hold up the role warps' next iteration
+                    if (do_search && lp.flow > 1) search_tile(S, sbase, lp, (uint32_t)k, ce, &S.gctr[(uint32_t)k % 3u], lane);
+                    __threadfence_block();
+                    bar_sync_n(b1, LZ_THREADS);
+                    if (do_hash) { hash_tile_n(S, (uint32_t)(k + 2), rtid, NRT); sweep_tables_n(S, (uint32_t)(k + 2), rtid, NRT); }
+                    if (rtid == 0) { S.gctr[(uint32_t)(k + 2) % 3u] = 0; __threadfence_block(); *(volatile uint32_t*)&S.b1_done = (uint32_t)(k + 2); }
+                    bar_sync_n(4u, NRT);
+                }
+                pf[7]++;
+            }
+        } else
         for (int k = -1; k <= (int)ntiles; k++) {
             const bool do_insert = k + 1 < (int)ntiles;
             const bool do_hash = k + 2 < (int)ntiles;
@@ -589,9 +704,9 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 if (do_insert) {
                     long long c0 = clock64();
                     const uint32_t t = (uint32_t)(k + 1);
-                    if (role == ROLE_INS0) insert_tile<0>(S, sbase, t, n_s, lane);
-                    else if (role == ROLE_INS1) insert_tile<1>(S, sbase, t, n_s, lane);
-                    else insert_tile<2>(S, sbase, t, n_s, lane);
+                    if (role == ROLE_INS0) insert_tile<0, false>(S, sbase, t, n_s, lane);
+                    else if (role == ROLE_INS1) insert_tile<1, false>(S, sbase, t, n_s, lane);
+                    else insert_tile<2, false>(S, sbase, t, n_s, lane);
                     pf[6] += (unsigned long long)(clock64() - c0);
                 }
             } else if (role == ROLE_LOAD) {
@@ -655,9 +770,11 @@ cudaError_t lz77_read_prof(unsigned long long* out16, int reset)
 
 cudaError_t lz77_configure()
 {
-    cudaError_t e = cudaFuncSetAttribute(k_lz77<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    cudaError_t e = cudaFuncSetAttribute(k_lz77<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_lz77<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    e = cudaFuncSetAttribute(k_lz77<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_lz77<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
 }
 
 void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
@@ -670,8 +787,9 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
     if (dict) { run = nchunks / (4u * (uint32_t)n_sm); run = run < 1u ? 1u : run > 4u ? 4u : run; }
     const uint32_t nruns = (nchunks + run - 1) / run;
     const uint32_t grid = nruns < (uint32_t)n_sm ? nruns : (uint32_t)n_sm;
-    if (lp.parse_warps == 16) k_lz77<16><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
-    else k_lz77<8><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
+    if (lp.parse_warps == 16) k_lz77<16, false><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
+    else if (lp.flow) k_lz77<8, true><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
+    else k_lz77<8, false><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
 }
 
 }  // namespace gzb

@@ -13,7 +13,7 @@ int main(int argc, char **argv)
     int hbits = 14, hsize = 1 << hbits;
     int32_t *head = malloc(4 * hsize), *link = malloc(4 * n);
     for (int i = 0; i < hsize; i++) head[i] = -1;
-    double hist[16] = {0}, cmp_at[16] = {0};
+    double hist[16] = {0}, cmp_at[16] = {0}, improved = 0, f2 = 0;
     double steps = 0, pass = 0, cmps = 0, cbytes = 0, gsteps = 0, gcmp = 0, gwords = 0, groups = 0, found6 = 0;
     int lsteps[32], lcmp[32], lwords[32];
     for (size_t p = 0; p < n; p++) {
@@ -26,7 +26,7 @@ int main(int argc, char **argv)
             st++;
             if (maxlen > best && s[c + best] == s[p + best]) {
                 int l = common_len(s + c, s + p, maxlen);
-                nc++; nw += l / 4 + 1; pass++; cbytes += l; cmp_at[st]++;
+                nc++; nw += l / 4 + 1; pass++; cbytes += l; cmp_at[st]++; if (l > best) improved++; if (maxlen > best + 1 && best >= 3 && s[c + best - 1] != s[p + best - 1]) f2++;
                 if (l > best) { best = l; if (l >= nice) break; if (good && !cut && best >= good) { d >>= 2; cut = 1; } }
             }
             c = link[c];
@@ -42,6 +42,7 @@ int main(int argc, char **argv)
     }
     printf("kind %d depth %d nice %d: per position: chain steps %.2f, compares %.2f, compared bytes %.1f, found>=6 %.3f | per group (max over lanes): steps %.2f, compares %.2f, compare words %.1f\n",
            kind, depth, nicep, steps / n, cmps / n, cbytes / n, found6 / n, gsteps / groups, gcmp / groups, gwords / groups);
+    printf("  compares that improved: %.3f per position; compares a second filter byte (best-1) would have skipped: %.3f\n", improved / n, f2 / n);
     printf("  steps histogram:"); for (int i = 0; i <= depth; i++) printf(" %d:%.3f", i, hist[i] / n); printf("\n  compares at step:"); for (int i = 1; i <= depth; i++) printf(" %d:%.3f", i, cmp_at[i] / n); printf("\n");
     return 0;
 }
