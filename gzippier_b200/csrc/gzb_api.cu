@@ -424,7 +424,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
     const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
     const uint32_t dsz = rs ? 0u : GZB_DICT;
-    const uint64_t HOST_BATCH = 128ull << 20;                      // multiple of both chunk sizes
+    const uint64_t HOST_BATCH = (getenv("GZB_HOST_BATCH_MB") ? (uint64_t)atoi(getenv("GZB_HOST_BATCH_MB")) : 512ull) << 20;   // multiple of both chunk sizes
     std::lock_guard<std::mutex> g(ctx->mu);
     CU(ctx, cudaSetDevice(ctx->device));
     const uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;

@@ -781,10 +781,19 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st)
 {
     if (nchunks == 0) return;
-    // chunks per run: up to 4 when there are enough chunks to keep every SM busy for several runs; independent
-    // chunks (--rsyncable: no dictionary) are never chained
+    // chunks per run: up to 4, whichever keeps the SMs busiest; independent chunks (--rsyncable: no dictionary) are
+    // never chained
+    // (cost of a choice: waves of runs over the SMs x tiles per run; the 16 dictionary tiles of a run are inserted
+    // but neither searched nor parsed, which makes them about as dear as 10 full ones)
     uint32_t run = 1;
-    if (dict) { run = nchunks / (4u * (uint32_t)n_sm); run = run < 1u ? 1u : run > 4u ? 4u : run; }
+    if (dict) {
+        uint64_t best_cost = ~0ull;
+        for (uint32_t r = 1; r <= 4u; r++) {
+            const uint64_t waves = ((nchunks + r - 1) / r + (uint32_t)n_sm - 1) / (uint32_t)n_sm;
+            const uint64_t cost = waves * (r * 64u + 10u);
+            if (cost < best_cost) { best_cost = cost; run = r; }
+        }
+    }
     const uint32_t nruns = (nchunks + run - 1) / run;
     const uint32_t grid = nruns < (uint32_t)n_sm ? nruns : (uint32_t)n_sm;
     if (lp.parse_warps == 16) k_lz77<16, false><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);
