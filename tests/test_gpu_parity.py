@@ -176,3 +176,40 @@ def test_large_roundtrip_properties(gz, orc, ctx):
     if ref is not None:
         mine, _ = ctx.deflate_host(d[: 64 << 20].copy(), 6)
         assert mine.size <= RATIO_TOL * (len(ref) - 18)
+
+
+def test_host_pipeline_batches_and_sub_batches(gz, orc, monkeypatch):
+    """The host path streams batches through two device slots, and a device call is cut into sub-batches chained by
+    a device-side cursor: with both made tiny, the bytes must still equal the one-shot result (and the model)."""
+    n = 23 * gz.CHUNK + 4321
+    d = gz.corpus("mixed", n, seed=31)
+    want = orc.engine_model(d, 6).tobytes()
+    want_rs = orc.engine_model(d, 6, rsyncable=True).tobytes()
+    monkeypatch.setenv("GZB_BATCH_CHUNKS", "3")          # read by gzb_create
+    c = gz.Context(0)
+    try:
+        for mb in ("1", "2", "512"):
+            monkeypatch.setenv("GZB_HOST_BATCH_MB", mb)  # read by every gzb_deflate_host call
+            raw, r = c.deflate_host(d, 6)
+            assert raw.tobytes() == want and r.crc32 == zlib.crc32(d.tobytes()) and r.in_bytes == n
+            raw, r = c.deflate_host(d, 6, gz.F_FINAL | gz.F_RSYNCABLE)
+            assert raw.tobytes() == want_rs and r.crc32 == zlib.crc32(d.tobytes())
+    finally:
+        c.close()
+
+
+@pytest.mark.parametrize("pw,flow", [("8", "0"), ("8", "1"), ("8", "2"), ("16", "0")])
+def test_kernel_variants_give_the_same_bytes(gz, orc, ctx, monkeypatch, pw, flow):
+    """k_lz77 is built in three variants (parser group of 8 or 16 warps; barrier-per-tile or flowing pipeline) chosen by
+    level; forced here at every level, none may change a byte."""
+    monkeypatch.setenv("GZB_PW", pw); monkeypatch.setenv("GZB_FLOW", flow)
+    for kind, n in (("text", 5 * gz.CHUNK + 777), ("binary", 2 * gz.CHUNK), ("random", gz.CHUNK + 1)):
+        d = gz.corpus(kind, n, seed=5)
+        for level in (1, 4, 6, 9):
+            raw, r = ctx.deflate_host(d, level)
+            assert raw.tobytes() == orc.engine_model(d, level).tobytes(), (kind, level)
+    # long runs of chained chunks (4 per CTA) at full occupancy
+    d = gz.corpus("text", 700 * gz.CHUNK + 99, seed=6)
+    raw, r = ctx.deflate_host(d, 6)
+    assert r.crc32 == zlib.crc32(d.tobytes()) and zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+    assert raw.tobytes() == orc.engine_model(d, 6).tobytes()
