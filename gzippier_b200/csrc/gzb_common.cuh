@@ -36,6 +36,7 @@ constexpr int      HDR_BYTES   = 608;             // worst case 14 + 57 + 316*14
 struct LevelParams {
     int depth, nice, max_lazy, lazy_parse, use_h3, use_h4;
     int parse_warps;                         // 8 or 16: size of k_lz77's parser group (no effect on the result)
+    int spin_ns;                             // k_lz77 (flow): sleep between two polls of a pipeline counter
     int flow;                                // k_lz77: search warps flow from tile to tile (no effect on the result)
 };
 

@@ -559,9 +559,9 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
 
 __device__ __forceinline__ void bar_sync_n(uint32_t id, uint32_t n) { asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive_n(uint32_t id, uint32_t n) { asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void wait_ge(const uint32_t* flag, uint32_t v, uint32_t lane)
+__device__ __forceinline__ void wait_ge(const uint32_t* flag, uint32_t v, uint32_t lane, uint32_t ns)
 {
-    if (lane == 0) while (*(volatile const uint32_t*)flag < v) __nanosleep(100);
+    if (lane == 0) while (*(volatile const uint32_t*)flag < v) __nanosleep(ns);
     __syncwarp();
     __threadfence_block();
 }
@@ -645,11 +645,16 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 uint32_t ce = 0;
                 if (do_search) { const uint32_t ci = ((uint32_t)k * TILE - D) / chunk; ce = min(D + (ci + 1u) * chunk, n_s); }
                 if (role == ROLE_SEARCH) {
-                    wait_ge(&S.b1_done, (uint32_t)max(k, 0), lane);
+                    const long long w0 = clock64();
+                    wait_ge(&S.b1_done, (uint32_t)max(k, 0), lane, (uint32_t)lp.spin_ns);
+                    const long long w1 = clock64();
+                    pf[1] += (unsigned long long)(w1 - w0);
                     if (do_search) {
-                        wait_ge(&S.ins_total, 3u * (uint32_t)(k + 1), lane);
-                        if (k - 2 >= (int)first_ctile) wait_ge(&S.parsed, (uint32_t)(k - 1 - (int)first_ctile), lane);
+                        wait_ge(&S.ins_total, 3u * (uint32_t)(k + 1), lane, (uint32_t)lp.spin_ns);
+                        const long long w2 = clock64();
+                        if (k - 2 >= (int)first_ctile) wait_ge(&S.parsed, (uint32_t)(k - 1 - (int)first_ctile), lane, (uint32_t)lp.spin_ns);
                         const long long ph0 = clock64();
+                        pf[2] += (unsigned long long)(w2 - w1); pf[3] += (unsigned long long)(ph0 - w2);
                         search_tile(S, sbase, lp, (uint32_t)k, ce, &S.gctr[(uint32_t)k % 3u], lane);
                         pf[0] += (unsigned long long)(clock64() - ph0);
                     }
