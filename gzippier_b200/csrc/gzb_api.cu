@@ -83,10 +83,10 @@ const LevelParams& level_params(int level)
     // good/lazy/nice: the reference's configuration_table (lib/zlib/deflate.c:134-146).
     // depth: candidates examined per position (every position is searched, chains keyed on 6 bytes).
     static const LevelParams t[10] = {
-        {0, 0, 0, 0, 0, 0},
-        {1, 8, 4, 0, 1, 1},   {2, 16, 5, 0, 1, 1},   {4, 32, 6, 0, 1, 1},
-        {4, 16, 4, 1, 1, 1},  {6, 32, 16, 1, 1, 1},  {8, 128, 16, 1, 1, 1},
-        {16, 128, 32, 1, 1, 1}, {32, 258, 128, 1, 1, 1}, {64, 258, 258, 1, 1, 1}};
+        {0, 0, 0, 0, 0, 0, 0, 0, 0},
+        {1, 8, 4, 0, 1, 1, 0, 0, 0},   {2, 16, 5, 0, 1, 1, 0, 0, 0},   {4, 32, 6, 0, 1, 1, 0, 0, 0},
+        {4, 16, 4, 1, 1, 1, 0, 0, 0},  {6, 32, 16, 1, 1, 1, 0, 0, 0},  {8, 128, 16, 1, 1, 1, 0, 0, 0},
+        {16, 128, 32, 1, 1, 1, 0, 0, 0}, {32, 258, 128, 1, 1, 1, 0, 0, 0}, {64, 258, 258, 1, 1, 1, 0, 0, 0}};
     return t[level];
 }
 
@@ -555,6 +555,20 @@ int gzb_crc32_host(gzb_ctx* ctx, uint32_t crc, const uint8_t* in, uint64_t n, ui
     }
     *crc_out = acc;
     return GZB_OK;
+}
+
+int gzb_host_alloc(gzb_ctx* ctx, uint64_t bytes, void** p)
+{
+    if (!ctx || !p) return GZB_E_ARG;
+    *p = nullptr;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return fail(ctx, GZB_E_CUDA, "cudaSetDevice");
+    if (cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); *p = nullptr; return fail(ctx, GZB_E_NOMEM, "cudaHostAlloc"); }
+    return GZB_OK;
+}
+
+void gzb_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
 }
 
 uint32_t gzb_crc32_combine(uint32_t crc1, uint32_t crc2, uint64_t len2)

@@ -1,25 +1,46 @@
 /* gzb_zip.c -- reference-facing host driver: what parallel_zip() does around the codec.
  *
  * Mirrors `off_t parallel_zip(int pack_level)` (reference src/parallel.c:699-834) and its
- * write_thread (:490-558) with the globals passed in gzb_zip_opts: read ifd on the fixed chunk
- * grid, look one batch ahead to know which batch is final (:764), hand every batch to the GPU
- * engine together with the 32 KiB that precede it (:767-774), write header / fragments in order /
- * trailer (:496-507, :538, :555-556), fold CRCs with crc32_combine (:544).
+ * write_thread (:490-558) with the globals passed in gzb_zip_opts.  The structure is the
+ * reference's own -- one reader, N compressors, one in-order writer, joined by bounded queues
+ * (src/parallel.c:106-143, 270-340) -- with the GPU engine where the compress threads stood:
+ *
+ *   reader   (caller's thread)  reads ifd in batches of BATCH bytes into pinned slots, keeps the
+ *                               32 KiB that precede a batch right in front of it (:767-774), and
+ *                               looks one batch ahead to know which one is final (:764)
+ *   workers  (2 per GPU)        each owns a context (its own streams): batch i goes to worker
+ *                               i mod W, which calls gzb_deflate_host on it.  Two workers per GPU
+ *                               put the copies of one batch under the kernels of the other.
+ *   writer   (one thread)       header, fragments in batch order, CRCs folded with
+ *                               crc32_combine (:544), trailer (:496-507, :538, :555-556)
+ *
+ * Batches are independent given their dictionary, so with n_gpus > 1 consecutive batches simply
+ * go to different GPUs: contiguous shards on chunk boundaries, no collective.
  * Differences by design: errors are reported, empty input yields the valid
  * 20-byte member instead of a deadlock (F4), and FNAME is the caller's choice (F5).
- *
- * With n_gpus > 1 every batch is cut into contiguous shards on chunk boundaries, one host thread
- * and one context per GPU, no collective: the host concatenates the shard bodies in order.
  */
+#define _GNU_SOURCE
 #include "gzb200.h"
 #include <errno.h>
+#include <fcntl.h>
 #include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
+#include <stdio.h>
+#include <sys/stat.h>
+#include <time.h>
 #include <unistd.h>
 
 #define MAX_GPUS 16
-#define SHARD_BYTES ((uint64_t)256 << 20)       /* per GPU per batch; multiple of the chunk size */
+#define MAX_WORKERS (2 * MAX_GPUS)
+#define MAX_SLOTS (MAX_WORKERS + 2)
+
+static uint64_t batch_bytes(void)               /* multiple of both chunk sizes */
+{
+    const char *e = getenv("GZB_ZIP_BATCH_MB");
+    uint64_t mb = e ? (uint64_t)atoi(e) : 128u;   /* slots are page-locked (~0.3 s per GiB): 4 slots of 2 x 128 MiB */
+    return (mb ? mb : 1u) << 20;
+}
 
 static ssize_t readn(int fd, uint8_t *buf, size_t len)
 {
@@ -42,17 +63,149 @@ static int writen(int fd, const uint8_t *buf, size_t len)
     return 0;
 }
 
-typedef struct {
-    gzb_ctx *ctx; int level; uint32_t flags;
-    const uint8_t *in; uint64_t n; const uint8_t *dict;
-    uint8_t *out; uint64_t out_cap; gzb_result res; int rc;
-} shard_job;
-
-static void *shard_worker(void *arg)
+/* A regular file is read by READERS threads with pread (one read() stream from the page cache is ~5 GB/s, a third
+ * of what one GPU takes); anything else -- a pipe, a tty -- sequentially, like the reference's readn (:66-84). */
+#define READERS 4
+typedef struct { int fd; uint8_t *buf; size_t len; off_t off; ssize_t got; } pread_job;
+static void *pread_worker(void *arg)
 {
-    shard_job *j = (shard_job *)arg;
-    j->rc = gzb_deflate_host(j->ctx, j->level, j->flags, j->in, j->n, j->dict, j->out, j->out_cap, &j->res);
+    pread_job *j = (pread_job *)arg;
+    size_t got = 0;
+    while (got < j->len) {
+        ssize_t r = pread(j->fd, j->buf + got, j->len - got, j->off + (off_t)got);
+        if (r < 0) { if (errno == EINTR) continue; j->got = -1; return NULL; }
+        if (r == 0) break;
+        got += (size_t)r;
+    }
+    j->got = (ssize_t)got;
     return NULL;
+}
+static ssize_t read_batch(int fd, uint8_t *buf, size_t len, int regular, off_t *pos)
+{
+    if (!regular) return readn(fd, buf, len);
+    pread_job j[READERS]; pthread_t th[READERS]; int started[READERS];
+    const size_t part = ((len / READERS) + 4095u) & ~(size_t)4095u;
+    for (int k = 0; k < READERS; k++) {
+        const size_t lo = (size_t)k * part < len ? (size_t)k * part : len;
+        const size_t hi = lo + part < len ? lo + part : len;
+        j[k].fd = fd; j[k].buf = buf + lo; j[k].len = hi - lo; j[k].off = *pos + (off_t)lo; j[k].got = 0;
+        started[k] = k > 0 && j[k].len && pthread_create(&th[k], NULL, pread_worker, &j[k]) == 0;
+        if (k > 0 && !started[k]) pread_worker(&j[k]);
+    }
+    pread_worker(&j[0]);
+    ssize_t total = 0; int shorted = 0;
+    for (int k = 0; k < READERS; k++) {
+        if (started[k]) pthread_join(th[k], NULL);
+        if (j[k].got < 0) return -1;
+        if (!shorted) total += j[k].got;            /* bytes after a short part belong to a file that grew: ignore */
+        if ((size_t)j[k].got < j[k].len) shorted = 1;
+    }
+    *pos += (off_t)total;
+    return total;
+}
+
+enum { S_FREE = 0, S_READ, S_DONE };
+
+typedef struct {
+    uint8_t *in;            /* pinned: GZB_DICT bytes of headroom, then the batch */
+    uint8_t *out;           /* pinned: gzb_bound(batch) */
+    uint64_t n;             /* bytes of the batch */
+    int state, final, have_dict;
+    gzb_result res;
+} slot;
+
+typedef struct pipe_s {
+    pthread_mutex_t mu; pthread_cond_t cv;
+    slot s[MAX_SLOTS]; int nslots, nworkers;
+    uint64_t n_read;        /* batches published by the reader */
+    int eof;                /* the reader is through: batch n_read - 1 is the last one */
+    int rc;                 /* first error; everybody stops */
+    int level; uint32_t flags; uint64_t batch, dict_sz, out_cap;
+    int ofd; gzb_zip_opts *o; uint32_t crc;
+    gzb_ctx *ctx[MAX_WORKERS];
+} pipe_t;
+
+typedef struct { pipe_t *p; int w; } worker_arg;
+
+static void fail(pipe_t *p, int rc)
+{
+    pthread_mutex_lock(&p->mu);
+    if (p->rc == GZB_OK) p->rc = rc;
+    pthread_cond_broadcast(&p->cv);
+    pthread_mutex_unlock(&p->mu);
+}
+
+static void *worker(void *arg)
+{
+    pipe_t *p = ((worker_arg *)arg)->p;
+    const int w = ((worker_arg *)arg)->w;
+    for (uint64_t i = (uint64_t)w;; i += (uint64_t)p->nworkers) {
+        slot *s = &p->s[i % (uint64_t)p->nslots];
+        pthread_mutex_lock(&p->mu);
+        /* batch i is there, and so is the knowledge whether it is the last one */
+        while (p->rc == GZB_OK && !(p->n_read > i + 1 || (p->eof && p->n_read > i)) && !(p->eof && p->n_read <= i))
+            pthread_cond_wait(&p->cv, &p->mu);
+        const int stop = p->rc != GZB_OK || (p->eof && p->n_read <= i);
+        const int final = p->eof && p->n_read == i + 1;
+        pthread_mutex_unlock(&p->mu);
+        if (stop) return NULL;
+        const uint8_t *data = s->in + GZB_DICT;
+        int rc = gzb_deflate_host(p->ctx[w], p->level, p->flags | (final ? GZB_F_FINAL : 0u), data, s->n,
+                                  (p->dict_sz && s->have_dict) ? data - p->dict_sz : NULL, s->out, p->out_cap, &s->res);
+        if (rc != GZB_OK) { fail(p, rc); return NULL; }
+        pthread_mutex_lock(&p->mu);
+        s->final = final; s->state = S_DONE;
+        pthread_cond_broadcast(&p->cv);
+        pthread_mutex_unlock(&p->mu);
+        if (final) return NULL;
+    }
+}
+
+static void *writer(void *arg)
+{
+    pipe_t *p = (pipe_t *)arg;
+    for (uint64_t i = 0;; i++) {
+        slot *s = &p->s[i % (uint64_t)p->nslots];
+        pthread_mutex_lock(&p->mu);
+        while (p->rc == GZB_OK && s->state != S_DONE) pthread_cond_wait(&p->cv, &p->mu);
+        const int stop = p->rc != GZB_OK;
+        pthread_mutex_unlock(&p->mu);
+        if (stop) return NULL;
+        if (writen(p->ofd, s->out, s->res.out_bytes)) { fail(p, GZB_E_IO); return NULL; }
+        p->crc = gzb_crc32_combine(p->crc, s->res.crc32, s->n);
+        p->o->bytes_in += s->n; p->o->bytes_out += s->res.out_bytes;
+        const int final = s->final;
+        pthread_mutex_lock(&p->mu);
+        s->state = S_FREE;
+        pthread_cond_broadcast(&p->cv);
+        pthread_mutex_unlock(&p->mu);
+        if (final) return NULL;
+    }
+}
+
+static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec; }
+
+/* Inputs that end within SMALL bytes -- most files a gzip ever sees -- take one call on pageable memory: no pinned
+ * slots (page-locking costs ~0.3 s per GiB), no threads. */
+#define SMALL ((size_t)32 << 20)
+static int zip_small(int ofd, gzb_zip_opts *o, uint32_t flags, const uint8_t *data, uint64_t n)
+{
+    gzb_ctx *ctx = NULL;
+    uint8_t *out = NULL, tr[8];
+    gzb_result r;
+    int rc = gzb_create(0, &ctx);
+    if (rc != GZB_OK) return rc;
+    const uint64_t cap = gzb_bound(n, flags);
+    if (!(out = (uint8_t *)malloc(cap))) rc = GZB_E_NOMEM;
+    if (rc == GZB_OK) rc = gzb_deflate_host(ctx, o->level, flags | GZB_F_FINAL, data, n, NULL, out, cap, &r);
+    if (rc == GZB_OK && writen(ofd, out, r.out_bytes)) rc = GZB_E_IO;
+    if (rc == GZB_OK) {
+        gzb_gzip_trailer(r.crc32, n, tr, sizeof(tr));
+        if (writen(ofd, tr, 8)) rc = GZB_E_IO;
+        o->bytes_in = n; o->bytes_out += r.out_bytes + 8;
+    }
+    free(out); gzb_destroy(ctx);
+    return rc;
 }
 
 int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
@@ -62,66 +215,109 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     if (ng > MAX_GPUS) ng = MAX_GPUS;
     if (ng > gzb_device_count()) ng = gzb_device_count();
     if (ng < 1) return GZB_E_NO_DEVICE;
-    const uint32_t flags = o->rsyncable ? GZB_F_RSYNCABLE : 0u;
-    const uint64_t dict_sz = o->rsyncable ? 0 : GZB_DICT;
-    const uint64_t batch = SHARD_BYTES * (uint64_t)ng;
-    gzb_ctx *ctx[MAX_GPUS] = {0};
-    uint8_t *buf[2] = {NULL, NULL}, *outb[MAX_GPUS] = {0};
-    uint8_t dict_keep[GZB_DICT];
-    int rc = GZB_OK, have_dict = 0;
-    uint8_t hdr[10 + 4096];
+    if (o->name && strlen(o->name) > 4000) return GZB_E_ARG;
+    const int verbose = getenv("GZB_ZIP_VERBOSE") != NULL;
+    const double t0 = now_s();
 
-    for (int g = 0; g < ng; g++) if ((rc = gzb_create(g, &ctx[g])) != GZB_OK) goto done;
-    for (int i = 0; i < 2; i++) if (!(buf[i] = (uint8_t *)malloc(batch ? batch : 1))) { rc = GZB_E_NOMEM; goto done; }
-    for (int g = 0; g < ng; g++) if (!(outb[g] = (uint8_t *)malloc(gzb_bound(SHARD_BYTES, flags)))) { rc = GZB_E_NOMEM; goto done; }
+    pipe_t P, *p = &P;
+    memset(p, 0, sizeof(*p));
+    struct stat st;
+    off_t pos = 0;
+    const int regular = fstat(ifd, &st) == 0 && S_ISREG(st.st_mode) && (pos = lseek(ifd, 0, SEEK_CUR)) >= 0;
+#ifdef F_SETPIPE_SZ
+    if (!regular) { (void)fcntl(ifd, F_SETPIPE_SZ, 1 << 20); (void)fcntl(ofd, F_SETPIPE_SZ, 1 << 20); }   /* pipes: fewer, larger transfers */
+#endif
+    pthread_mutex_init(&p->mu, NULL); pthread_cond_init(&p->cv, NULL);
+    p->level = o->level; p->flags = o->rsyncable ? GZB_F_RSYNCABLE : 0u;
+    p->dict_sz = o->rsyncable ? 0 : GZB_DICT;
+    p->batch = batch_bytes(); p->out_cap = gzb_bound(p->batch, p->flags);
+    p->nworkers = 2 * ng; p->nslots = p->nworkers + 2;
+    p->ofd = ofd; p->o = o; p->rc = GZB_OK;
+    pthread_t th[MAX_WORKERS], wth; worker_arg wa[MAX_WORKERS];
+    int nth = 0, have_writer = 0, rc = GZB_OK;
+    uint8_t hdr[10 + 4096], *peek = NULL;
+    double t_setup = t0, t_stream = t0;
 
-    if (o->name && strlen(o->name) > 4000) { rc = GZB_E_ARG; goto done; }
     int hn = gzb_gzip_header(o->level, o->mtime, o->name, hdr, sizeof(hdr));
     if (hn < 0) { rc = hn; goto done; }
     if (writen(ofd, hdr, (size_t)hn)) { rc = GZB_E_IO; goto done; }
     o->bytes_in = 0; o->bytes_out = (uint64_t)hn;
 
-    uint32_t crc = 0;
-    int cur = 0;
-    ssize_t got = readn(ifd, buf[cur], batch);
-    if (got < 0) { rc = GZB_E_IO; goto done; }
-    for (;;) {
-        ssize_t next = ((uint64_t)got == batch) ? readn(ifd, buf[cur ^ 1], batch) : 0;   /* look ahead: who is final? */
-        if (next < 0) { rc = GZB_E_IO; goto done; }
-        const int final_batch = (next == 0);
-        /* shards on chunk boundaries */
-        shard_job jobs[MAX_GPUS]; pthread_t th[MAX_GPUS]; int nj = 0;
-        uint64_t off = 0;
-        do {
-            uint64_t nb = (uint64_t)got - off < SHARD_BYTES ? (uint64_t)got - off : SHARD_BYTES;
-            shard_job *j = &jobs[nj];
-            memset(j, 0, sizeof(*j));
-            j->ctx = ctx[nj]; j->level = o->level;
-            j->in = buf[cur] + off; j->n = nb;
-            j->dict = dict_sz ? (off ? buf[cur] + off - dict_sz : (have_dict ? dict_keep : NULL)) : NULL;
-            j->flags = flags | ((final_batch && off + nb == (uint64_t)got) ? GZB_F_FINAL : 0u);
-            j->out = outb[nj]; j->out_cap = gzb_bound(SHARD_BYTES, flags);
-            off += nb; nj++;
-        } while (off < (uint64_t)got);
-        for (int k = 1; k < nj; k++) if (pthread_create(&th[k], NULL, shard_worker, &jobs[k])) { jobs[k].rc = GZB_E_NOMEM; th[k] = 0; shard_worker(&jobs[k]); }
-        shard_worker(&jobs[0]);
-        for (int k = 1; k < nj; k++) if (th[k]) pthread_join(th[k], NULL);
-        for (int k = 0; k < nj; k++) {
-            if (jobs[k].rc != GZB_OK) { rc = jobs[k].rc; goto done; }
-            if (writen(ofd, jobs[k].out, jobs[k].res.out_bytes)) { rc = GZB_E_IO; goto done; }
-            crc = gzb_crc32_combine(crc, jobs[k].res.crc32, jobs[k].n);
-            o->bytes_in += jobs[k].n; o->bytes_out += jobs[k].res.out_bytes;
-        }
-        if (final_batch) break;
-        if (dict_sz) { memcpy(dict_keep, buf[cur] + (uint64_t)got - dict_sz, dict_sz); have_dict = 1; }   /* a non-final batch is full */
-        cur ^= 1; got = next;
+    /* look at the first SMALL bytes: is that all there is? */
+    const size_t peek_len = SMALL < p->batch ? SMALL : (size_t)p->batch;
+    if (!(peek = (uint8_t *)malloc(peek_len))) { rc = GZB_E_NOMEM; goto done; }
+    ssize_t pk = read_batch(ifd, peek, peek_len, regular, &pos);
+    if (pk < 0) { rc = GZB_E_IO; goto done; }
+    if ((size_t)pk < peek_len) { rc = zip_small(ofd, o, p->flags, peek, (uint64_t)pk); goto done; }
+
+    for (int w = 0; w < p->nworkers; w++) if ((rc = gzb_create(w % ng, &p->ctx[w])) != GZB_OK) goto done;
+    for (int w = 0; w < p->nworkers; w++) {
+        wa[w].p = p; wa[w].w = w;
+        if (pthread_create(&th[w], NULL, worker, &wa[w])) { fail(p, GZB_E_NOMEM); break; }
+        nth++;
     }
-    uint8_t tr[8];
-    gzb_gzip_trailer(crc, o->bytes_in, tr, sizeof(tr));
-    if (writen(ofd, tr, 8)) { rc = GZB_E_IO; goto done; }
-    o->bytes_out += 8;
+    if (pthread_create(&wth, NULL, writer, p)) fail(p, GZB_E_NOMEM); else have_writer = 1;
+    t_setup = now_s();
+
+    /* the reader */
+    for (uint64_t i = 0;; i++) {
+        slot *s = &p->s[i % (uint64_t)p->nslots];
+        if (!s->in) {                             /* slots are page-locked on first use, under the work of the earlier batches */
+            int arc = gzb_host_alloc(p->ctx[0], GZB_DICT + p->batch, (void **)&s->in);
+            if (arc == GZB_OK) arc = gzb_host_alloc(p->ctx[0], p->out_cap, (void **)&s->out);
+            if (arc != GZB_OK) { fail(p, arc); break; }
+        }
+        pthread_mutex_lock(&p->mu);
+        while (p->rc == GZB_OK && s->state != S_FREE) pthread_cond_wait(&p->cv, &p->mu);
+        const int stop = p->rc != GZB_OK;
+        pthread_mutex_unlock(&p->mu);
+        if (stop) break;
+        size_t pre = 0;
+        if (i == 0) { memcpy(s->in + GZB_DICT, peek, (size_t)pk); pre = (size_t)pk; }
+        ssize_t got = pre < p->batch ? read_batch(ifd, s->in + GZB_DICT + pre, p->batch - pre, regular, &pos) : 0;
+        if (got < 0) { fail(p, GZB_E_IO); break; }
+        got += (ssize_t)pre;
+        if (got == 0 && i > 0) {                  /* nothing after a full batch: the previous one was the last */
+            pthread_mutex_lock(&p->mu);
+            p->eof = 1; pthread_cond_broadcast(&p->cv);
+            pthread_mutex_unlock(&p->mu);
+            break;
+        }
+        s->n = (uint64_t)got; s->have_dict = 0;
+        if (i > 0 && p->dict_sz) {                /* the dictionary of a batch: the tail of the one before (which was full) */
+            const slot *prev = &p->s[(i - 1) % (uint64_t)p->nslots];
+            memcpy(s->in + GZB_DICT - p->dict_sz, prev->in + GZB_DICT + prev->n - p->dict_sz, p->dict_sz);
+            s->have_dict = 1;
+        }
+        pthread_mutex_lock(&p->mu);
+        s->state = S_READ; p->n_read = i + 1;
+        if ((uint64_t)got < p->batch) p->eof = 1; /* a short batch is the last */
+        pthread_cond_broadcast(&p->cv);
+        const int last = p->eof;
+        pthread_mutex_unlock(&p->mu);
+        if (last) break;
+    }
+    if (p->rc != GZB_OK) {                        /* wake everybody who waits for a batch that will not come */
+        pthread_mutex_lock(&p->mu); p->eof = 1; pthread_cond_broadcast(&p->cv); pthread_mutex_unlock(&p->mu);
+    }
+    for (int w = 0; w < nth; w++) pthread_join(th[w], NULL);
+    if (have_writer) pthread_join(wth, NULL);
+    rc = p->rc;
+    if (rc == GZB_OK) {
+        uint8_t tr[8];
+        gzb_gzip_trailer(p->crc, o->bytes_in, tr, sizeof(tr));
+        if (writen(ofd, tr, 8)) rc = GZB_E_IO; else o->bytes_out += 8;
+    }
+    t_stream = now_s();
 done:
-    for (int g = 0; g < ng; g++) { if (ctx[g]) gzb_destroy(ctx[g]); free(outb[g]); }
-    free(buf[0]); free(buf[1]);
+    free(peek);
+    for (int i = 0; i < p->nslots; i++) { if (p->s[i].in) gzb_host_free(p->s[i].in); if (p->s[i].out) gzb_host_free(p->s[i].out); }
+    for (int w = 0; w < p->nworkers; w++) if (p->ctx[w]) gzb_destroy(p->ctx[w]);
+    pthread_mutex_destroy(&p->mu); pthread_cond_destroy(&p->cv);
+    if (regular) lseek(ifd, pos, SEEK_SET);          /* leave the descriptor where a sequential reader would */
+    if (verbose)
+        fprintf(stderr, "gzb_zip_fd: rc %d, %llu -> %llu bytes; contexts + threads %.3f s, read/compress/write %.3f s (%.2f GB/s), teardown %.3f s\n",
+                rc, (unsigned long long)o->bytes_in, (unsigned long long)o->bytes_out, t_setup - t0, t_stream - t_setup,
+                t_stream > t_setup ? (double)o->bytes_in / (t_stream - t_setup) / 1e9 : 0.0, now_s() - t_stream);
     return rc;
 }

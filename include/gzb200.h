@@ -147,6 +147,12 @@ typedef struct gzb_zip_opts {
 } gzb_zip_opts;
 int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *opts);
 
+/* Page-locked host memory for the buffers handed to gzb_deflate_host (which then DMAs straight from / to them
+ * instead of staging).  Stands where the reference's buffer pools stood (src/parallel.c:169-259: get_space /
+ * drop_space / grow_space -- fixed sizes here, gzb_bound() makes growing unnecessary). */
+int gzb_host_alloc(gzb_ctx *ctx, uint64_t bytes, void **p);
+void gzb_host_free(void *p);
+
 /* ---- synthetic corpora for bench/tests (host only, csrc/corpus.c) ---- */
 #define GZB_CORPUS_TEXT    0
 #define GZB_CORPUS_ZIPF    1
