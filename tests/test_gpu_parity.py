@@ -213,3 +213,41 @@ def test_kernel_variants_give_the_same_bytes(gz, orc, ctx, monkeypatch, pw, flow
     raw, r = ctx.deflate_host(d, 6)
     assert r.crc32 == zlib.crc32(d.tobytes()) and zlib.decompress(raw.tobytes(), -15) == d.tobytes()
     assert raw.tobytes() == orc.engine_model(d, 6).tobytes()
+
+
+def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
+    """gzb_zip_fd above its small-input threshold: reader / worker contexts / in-order writer over many batches, from a
+    regular file (parallel pread) and from a pipe; the member must be header + the one-shot body + trailer."""
+    import threading
+    n = (37 << 20) + 12345
+    d = gz.corpus("mixed", n, seed=41)
+    want = orc.engine_model(d, 6).tobytes()
+    src = tmp_path / "big.bin"; src.write_bytes(d.tobytes())
+    for mb in ("1", "3", "128"):
+        monkeypatch.setenv("GZB_ZIP_BATCH_MB", mb)
+        dst = tmp_path / f"out{mb}.gz"
+        with open(src, "rb") as fi, open(dst, "wb") as fo:
+            bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
+            assert fi.tell() == n                       # the descriptor is left at EOF, as after a sequential read
+        m = dst.read_bytes()
+        assert bi == n and bo == len(m)
+        assert m[:10] == gz.gzip_header(6) and m[10:-8] == want and m[-8:] == gz.gzip_trailer(zlib.crc32(d.tobytes()), n)
+    # a pipe on both sides
+    monkeypatch.setenv("GZB_ZIP_BATCH_MB", "2")
+    r_in, w_in = os.pipe(); r_out, w_out = os.pipe()
+    got = bytearray()
+    def feed():
+        with os.fdopen(w_in, "wb") as f: f.write(d.tobytes())
+    def drain():
+        with os.fdopen(r_out, "rb") as f: got.extend(f.read())
+    t1 = threading.Thread(target=feed); t2 = threading.Thread(target=drain); t1.start(); t2.start()
+    bi, bo = gz.zip_fd(r_in, w_out, level=6)
+    os.close(w_out); os.close(r_in); t1.join(); t2.join()
+    assert bi == n and bytes(got[10:-8]) == want and zlib.decompress(bytes(got), 31) == d.tobytes()
+    # errors are reported (SURVEY F7): unwritable output
+    with open(src, "rb") as fi, open(tmp_path / "ro", "wb") as fo:
+        pass
+    with open(src, "rb") as fi, open(tmp_path / "ro", "rb") as fo:
+        with pytest.raises(gz.GzbError) as e:
+            gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
+        assert e.value.code == gz.E_IO
