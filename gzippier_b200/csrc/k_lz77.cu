@@ -444,6 +444,7 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
         if (gtid == 0) { S.blk++; S.blk_tok0 = S.ntok; S.blk_in0 = S.entry - D; }
         group_sync();
     }
+    const long long pt0 = clock64();
     const int entry = (int)S.entry;                       // >= base by construction
     const int lim = hi_w - base;                          // positions [0, lim) of the tile can start a token
     constexpr int NWIN = TILE / 32, WPW = NWIN / PARSE_WARPS;
@@ -475,6 +476,7 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
         wexit[o] = (uint16_t)x;
         if (lane == 0) went[w] = (uint16_t)TILE;
     }
+    const long long pt1 = clock64();
     group_sync();
     // 2.
     if (gtid == 0) {
@@ -485,6 +487,7 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
         if (last && e == base + TILE && e < (int)n_s) { extra = 1; e += 1; }   // final byte of a full last tile
         S.entry = (uint32_t)e; S.extra_lit = extra;
     }
+    const long long pt2 = clock64();
     group_sync();
     // 3.
 #pragma unroll
@@ -504,6 +507,7 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
         }
         if (lane == 0) S.masks[w] = m;
     }
+    const long long pt3 = clock64();
     group_sync();
     if (warp == 0) {
         const uint32_t c0 = (uint32_t)__popc(S.masks[2 * lane]), c1 = (uint32_t)__popc(S.masks[2 * lane + 1]);
@@ -538,8 +542,11 @@ __device__ void parse_emit_tile(Smem& S, const LevelParams& lp, int k, uint32_t 
             tok[ntok0 + S.seg_prefix[TILE / 32]] = tv;
         }
     }
+    const long long pt4 = clock64();
     group_sync();
     if (gtid == 0) {
+        atomicAdd(&g_lzprof[12], (unsigned long long)(pt1 - pt0)); atomicAdd(&g_lzprof[13], (unsigned long long)(pt2 - pt1));
+        atomicAdd(&g_lzprof[14], (unsigned long long)(pt3 - pt2)); atomicAdd(&g_lzprof[15], (unsigned long long)(pt4 - pt3));
         S.ntok += S.seg_prefix[TILE / 32] + S.extra_lit; S.extra_lit = 0;
         // the parse of the next tile starts at this tile's last position, whose slot in mlen/mdist the search that runs
         // beside it rewrites: stash it now
