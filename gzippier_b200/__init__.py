@@ -10,8 +10,8 @@ import ctypes, os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgzb200.so")
 
-OK, E_ARG, E_LEVEL, E_NOMEM, E_CUDA, E_NO_DEVICE, E_OUT_FULL, E_IO = 0, -1, -2, -3, -4, -5, -6, -7
-F_FINAL, F_RSYNCABLE = 1, 2
+OK, E_ARG, E_LEVEL, E_NOMEM, E_CUDA, E_NO_DEVICE, E_OUT_FULL, E_IO, E_VERIFY = 0, -1, -2, -3, -4, -5, -6, -7, -8
+F_FINAL, F_RSYNCABLE, F_VERIFY = 1, 2, 4
 CHUNK, DICT, RSYNC_CHUNK = 131072, 32768, 16384
 CORPUS = {"text": 0, "zipf": 1, "binary": 2, "random": 3, "mixed": 4}
 

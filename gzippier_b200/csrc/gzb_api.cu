@@ -124,6 +124,7 @@ const char* gzb_strerror(int code)
     case GZB_E_NO_DEVICE: return "no usable CUDA device (there is no CPU fallback)";
     case GZB_E_OUT_FULL: return "output buffer smaller than gzb_bound()";
     case GZB_E_IO: return "I/O error";
+    case GZB_E_VERIFY: return "GZB_F_VERIFY: the output does not decode back to the input";
     default: return "unknown error";
     }
 }
@@ -283,10 +284,23 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
         if (timed) { CU(ctx, cudaEventRecord(ev[4], st)); }
         launch_pack(d_in + off, chunk, ctx->scr.tokens, ctx->scr.blocks, ctx->scr.chunks, nch, bpc, d_out, st);
         if (timed) { CU(ctx, cudaEventRecord(ev[5], st)); ctx->n_sub_timed = (int)sb + 1; }
+        if ((flags & GZB_F_VERIFY) && sb == 0 && getenv("GZB_DEBUG_CORRUPT_AT"))      // fault injection for the tests of k_verify
+            CU(ctx, cudaMemsetAsync(d_out + strtoull(getenv("GZB_DEBUG_CORRUPT_AT"), nullptr, 10), 0xA5, 1, st));
+        if (flags & GZB_F_VERIFY)
+            launch_verify(d_in + off, chunk, dict, h, ctx->scr.chunks, nch, d_out, fin, c0, ctx->d_cursor, st);
     }
     CU(ctx, cudaGetLastError());
     CU(ctx, cudaMemcpyAsync(ctx->h_cursor, ctx->d_cursor, sizeof(Cursor), cudaMemcpyDeviceToHost, st));
     return GZB_OK;
+}
+
+int verify_status(gzb_ctx* ctx, const Cursor& c)
+{
+    if (c.verify_bad == 0u) return GZB_OK;
+    char msg[160];
+    snprintf(msg, sizeof(msg), "verify: %u chunk(s) do not decode back to their input; first: chunk %llu, code %u (k_verify.cu)",
+             c.verify_bad, (unsigned long long)c.verify_first, c.verify_code);
+    return fail(ctx, GZB_E_VERIFY, msg);
 }
 
 void cursor_to_result(const Cursor& c, gzb_result* r)
@@ -320,6 +334,10 @@ int gzb_deflate_wait(gzb_ctx* ctx, gzb_result* result)
     CU(ctx, cudaStreamSynchronize(ctx->pending_stream));
     if (ctx->h_cursor->in_bytes != ctx->pending_n) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
     if (result) cursor_to_result(*ctx->h_cursor, result);
+    if (ctx->h_cursor->status == GZB_OK && ctx->h_cursor->verify_bad) {
+        if (result) result->status = GZB_E_VERIFY;
+        return verify_status(ctx, *ctx->h_cursor);
+    }
     return ctx->h_cursor->status;
 }
 
@@ -485,6 +503,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
         CU(ctx, cudaStreamSynchronize(ctx->stream));                        // out_bytes of batch i is known now
         const Cursor c = *ctx->h_cursor;
         if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
+        if (c.verify_bad) return verify_status(ctx, c);
         if (c.in_bytes != nb) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
         if (opos + c.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
         if (c.out_bytes) CU(ctx, cudaMemcpyAsync(pin_out ? out + opos : ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));

@@ -82,6 +82,9 @@ struct Cursor {
     uint32_t n_chunks;
     uint32_t n_blocks;
     int32_t  status;
+    uint32_t verify_bad;      // GZB_F_VERIFY: chunks whose fragment does not decode back to their input (k_verify)
+    uint32_t verify_code;     // ... what was wrong with the first one found (codes in k_verify.cu)
+    uint64_t verify_first;    // ... and its index
 };
 
 // ---- token format: bit31 = match; match: (len-3) << 16 | (dist-1); literal: byte ----
@@ -162,6 +165,8 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st);
 void launch_huffman(BlockRec* blocks, const ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, cudaStream_t st);
 void launch_layout(BlockRec* blocks, ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, int final, Cursor* cur, const uint32_t* d_tab, cudaStream_t st);
+void launch_verify(const uint8_t* in, uint32_t chunk, uint32_t dict, uint32_t halo, const ChunkRec* chunks, uint32_t nchunks,
+                   const uint8_t* out, int final, uint64_t chunk0, Cursor* cur, cudaStream_t st);
 void launch_pack(const uint8_t* in, uint32_t chunk, const uint32_t* tokens, const BlockRec* blocks, const ChunkRec* chunks,
                  uint32_t nchunks, uint32_t bpc, uint8_t* out, cudaStream_t st);
 cudaError_t lz77_configure();

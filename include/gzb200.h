@@ -36,6 +36,7 @@ extern "C" {
 #define GZB_E_NO_DEVICE  (-5)   /* no usable CUDA device: there is no CPU fallback      */
 #define GZB_E_OUT_FULL   (-6)   /* out_cap < gzb_bound(n)                               */
 #define GZB_E_IO         (-7)   /* read()/write() failed in the host driver             */
+#define GZB_E_VERIFY     (-8)   /* GZB_F_VERIFY: the output did not decode back to the input */
 
 /* ---- the reference's chunk grid (src/parallel.c:13-15) ---- */
 #define GZB_CHUNK        131072u   /* IN_BUF_SIZE                                       */
@@ -46,6 +47,9 @@ extern "C" {
 #define GZB_F_FINAL       1u    /* this call ends the deflate stream: BFINAL on the last block
                                    (the job with more==0, src/parallel.c:645-649)          */
 #define GZB_F_RSYNCABLE   2u    /* 16 KiB independent chunks (src/parallel.c:333,767)      */
+#define GZB_F_VERIFY      4u    /* decode every fragment again on the device and compare it with the input before
+                                   returning (what `gzip -t` after the fact does through src/unzip.c:254-370, chunk
+                                   parallel because our fragment boundaries are known): GZB_E_VERIFY on a mismatch */
 
 typedef struct gzb_ctx gzb_ctx;
 

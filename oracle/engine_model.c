@@ -306,7 +306,7 @@ void gzm_plan_block(const uint32_t *lfreq_in, const uint32_t *dfreq, uint32_t in
     if (sto_b <= best) B->type = 0;
     else if (sta_b <= dyn_b) B->type = 1;
     else B->type = 2;
-    if (B->type == 1) { memcpy(B->llen, sl, 286); memcpy(B->dlen, sd, 30); }
+    if (B->type == 1) { memcpy(B->llen, sl, 288);   /* all 288: 286 and 287 take part in the code (RFC 1951 3.2.6) */ memcpy(B->dlen, sd, 30); }
     gzm_huff_codes(B->llen, B->type == 1 ? 288 : 286, 15, B->lcode);
     gzm_huff_codes(B->dlen, 30, 15, B->dcode);
 }

@@ -44,3 +44,21 @@ def test_model_rsyncable(gz, orc, golden):
     raw = orc.engine_model(d, 6, rsyncable=True)
     assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
     assert raw.size <= 1.03 * (e["rsyncable_parallel_6"] - 18)
+
+
+def test_model_static_blocks_with_high_literals(gz, orc):
+    """Static blocks carrying literals 144..255 (9-bit codes, which depend on symbols 286/287 being part of the code,
+    RFC 1951 3.2.6): tiny binary inputs and a tiny last chunk after incompressible ones."""
+    import numpy as np
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 3, 5, 17, 40):
+        for _ in range(8):
+            d = rng.integers(144, 256, n, dtype=np.uint8)
+            for level in (1, 6, 9):
+                raw = orc.engine_model(d, level)
+                assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+                assert orc.inflate(raw, n).tobytes() == d.tobytes()
+    for n in (2 * 131072 + 1, 2 * 131072 + 5, 131072 + 3):
+        d = gz.corpus("random", n, seed=9)
+        raw = orc.engine_model(d, 6)
+        assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()

@@ -251,3 +251,37 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
         with pytest.raises(gz.GzbError) as e:
             gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
         assert e.value.code == gz.E_IO
+
+
+def test_device_side_verify(gz, orc, ctx, monkeypatch):
+    """GZB_F_VERIFY: every fragment is decoded again on the device and compared with the input.  It must
+    pass on good output of every kind of block and catch a single corrupted byte anywhere."""
+    import torch
+    V = gz.F_FINAL | gz.F_VERIFY
+    for kind, n in (("text", 9 * gz.CHUNK + 77), ("binary", 3 * gz.CHUNK), ("random", 2 * gz.CHUNK + 5), ("mixed", 5 * gz.CHUNK + 1),
+                    ("text", 1), ("text", 70000)):
+        d = gz.corpus(kind, n, seed=9)
+        for level in (1, 6, 9):
+            raw, r = ctx.deflate_host(d, level, V)
+            assert r.status == gz.OK and raw.tobytes() == orc.engine_model(d, level).tobytes()
+        raw, r = ctx.deflate_host(d, 6, V | gz.F_RSYNCABLE)
+        assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+    # shards with a halo, non-final calls
+    n = 6 * gz.CHUNK + 123
+    d = gz.corpus("text", n, seed=10); t = torch.from_numpy(d).cuda()
+    out = torch.empty(gz.bound(n), dtype=torch.uint8, device="cuda")
+    r = ctx.deflate_device(t[2 * gz.CHUNK:], n - 2 * gz.CHUNK, out, 6, flags=V, halo=gz.DICT)
+    r = ctx.deflate_device(t, 2 * gz.CHUNK, out, 6, flags=gz.F_VERIFY)
+    # a corrupted byte is caught wherever it is
+    d = gz.corpus("text", 4 * gz.CHUNK, seed=11)
+    raw, r = ctx.deflate_host(d, 6, V)
+    for at in (0, 5, raw.size // 3, raw.size // 2, raw.size - 2):
+        monkeypatch.setenv("GZB_DEBUG_CORRUPT_AT", str(at))
+        if raw[at] == 0xA5:
+            continue
+        with pytest.raises(gz.GzbError) as e:
+            ctx.deflate_host(d, 6, V)
+        assert e.value.code == gz.E_VERIFY, at
+    monkeypatch.delenv("GZB_DEBUG_CORRUPT_AT")
+    raw2, _ = ctx.deflate_host(d, 6, V)
+    assert raw2.tobytes() == raw.tobytes()
