@@ -151,6 +151,9 @@ def main():
     raw = d_out[: r.out_bytes].cpu().numpy()
     if world == 1:
         assert zlib.decompress(raw.tobytes(), -15) == host.tobytes(), "round trip failed"
+    # every rank: the device-side round trip of its own shard (k_verify; raises GzbError(E_VERIFY) on a mismatch)
+    rv = ctx.deflate_device(d_in, n, d_out, a.level, flags=flags | gz.F_VERIFY, halo=halo, stream=stream.cuda_stream)
+    assert rv.out_bytes == r.out_bytes and rv.crc32 == r.crc32
     assert r.crc32 == zlib.crc32(host[halo:].tobytes()), "CRC mismatch"
     out_bytes = r.out_bytes
 
