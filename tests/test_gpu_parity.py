@@ -285,3 +285,18 @@ def test_device_side_verify(gz, orc, ctx, monkeypatch):
     monkeypatch.delenv("GZB_DEBUG_CORRUPT_AT")
     raw2, _ = ctx.deflate_host(d, 6, V)
     assert raw2.tobytes() == raw.tobytes()
+
+
+def test_more_than_4_gib_in_one_call(gz, ctx):
+    """64-bit offsets everywhere and ISIZE mod 2^32 (src/parallel.c:60,545): 4 GiB + 3 chunks + 11 bytes in one device call,
+    checked by the device-side round trip, the CRC and a zlib decode of the last fragments."""
+    import torch
+    n = (4 << 30) + 3 * gz.CHUNK + 11
+    d = gz.corpus("text", n, seed=13)
+    t = torch.from_numpy(d).cuda()
+    out = torch.empty(gz.bound(n), dtype=torch.uint8, device="cuda")
+    r = ctx.deflate_device(t, n, out, 1, flags=gz.F_FINAL | gz.F_VERIFY)
+    assert r.in_bytes == n and r.crc32 == zlib.crc32(memoryview(d))
+    assert gz.gzip_trailer(r.crc32, r.in_bytes)[4:] == (n % (1 << 32)).to_bytes(4, "little")
+    raw = out[: r.out_bytes].cpu().numpy().tobytes()
+    assert zlib.decompress(raw, -15, ) [-1000:] == d[-1000:].tobytes()
