@@ -9,7 +9,7 @@
 // searched in parallel (one lane per position), and the greedy/lazy parse -- a pure function
 // next(p) of the per-position matches -- is evaluated with pointer doubling instead of a walk.
 //
-// One persistent CTA (1024 threads, ~226 KB shared memory) per SM takes runs of up to 4
+// One persistent CTA (1024 threads, ~226 KB shared memory) per SM takes runs of up to 8
 // consecutive chunks from an atomic counter and streams through them: the tables at the end of
 // a chunk ARE the next chunk's dictionary, so only the first chunk of a run inserts its 32 KiB
 // dictionary.  Per tile k the CTA runs three things at once (one barrier per tile):
@@ -793,14 +793,15 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st)
 {
     if (nchunks == 0) return;
-    // chunks per run: up to 4, whichever keeps the SMs busiest; independent chunks (--rsyncable: no dictionary) are
+    // chunks per run: up to 8, whichever keeps the SMs busiest; independent chunks (--rsyncable: no dictionary) are
     // never chained
     // (cost of a choice: waves of runs over the SMs x tiles per run; the 16 dictionary tiles of a run are inserted
     // but neither searched nor parsed, which makes them about as dear as 10 full ones)
     uint32_t run = 1;
+    const int max_run = getenv("GZB_MAX_RUN") ? atoi(getenv("GZB_MAX_RUN")) : 8;
     if (dict) {
         uint64_t best_cost = ~0ull;
-        for (uint32_t r = 1; r <= 4u; r++) {
+        for (uint32_t r = 1; r <= (uint32_t)max_run; r++) {
             const uint64_t waves = ((nchunks + r - 1) / r + (uint32_t)n_sm - 1) / (uint32_t)n_sm;
             const uint64_t cost = waves * (r * 64u + 10u);
             if (cost < best_cost) { best_cost = cost; run = r; }
