@@ -17,7 +17,8 @@ for rep in range(3):
     print(f"zip_fd file->file  L{level} {ngpu} GPU: {bi / dt / 1e9:6.2f} GB/s  ({bi} -> {bo} bytes, {dt * 1e3:.0f} ms incl. context creation)", flush=True)
 m = open(dst, "rb").read()
 assert int.from_bytes(m[-8:-4], "little") == crc and int.from_bytes(m[-4:], "little") == n % (1 << 32)
-t = time.time(); ok = zlib.decompress(m[: 64 << 20] if False else m, 31) == d.tobytes(); print("round trip (zlib):", ok, f"{time.time() - t:.1f}s", flush=True)
+if mib <= 4096:
+    t = time.time(); ok = zlib.decompress(m, 31) == d.tobytes(); print("round trip (zlib):", ok, f"{time.time() - t:.1f}s", flush=True)
 exe = os.path.join(os.path.dirname(gz.LIB_PATH), "gzb200")
 t = time.time(); subprocess.run(f"cat {src} | {exe} -{level} > /dev/null", shell=True, check=True); dt = time.time() - t
 print(f"cat | gzb200 -{level} > /dev/null: {n / dt / 1e9:6.2f} GB/s", flush=True)
