@@ -27,7 +27,8 @@ class StageMs(ctypes.Structure):
 
 class ZipOpts(ctypes.Structure):
     _fields_ = [("level", ctypes.c_int), ("rsyncable", ctypes.c_int), ("n_gpus", ctypes.c_int), ("name", ctypes.c_char_p),
-                ("mtime", ctypes.c_uint32), ("bytes_in", ctypes.c_uint64), ("bytes_out", ctypes.c_uint64)]
+                ("mtime", ctypes.c_uint32), ("bytes_in", ctypes.c_uint64), ("bytes_out", ctypes.c_uint64),
+                ("members", ctypes.c_int)]
 
 
 class GzbError(RuntimeError):
@@ -192,9 +193,11 @@ def _cap(t):
     return t.numel() * t.element_size()
 
 
-def zip_fd(ifd: int, ofd: int, level: int = 6, rsyncable: bool = False, n_gpus: int = 1, name: bytes | None = None, mtime: int = 0):
-    """Mirror of the reference's parallel_zip(): read ifd to EOF, write one gzip member to ofd."""
-    o = ZipOpts(level, int(rsyncable), n_gpus, name, mtime, 0, 0)
+def zip_fd(ifd: int, ofd: int, level: int = 6, rsyncable: bool = False, n_gpus: int = 1, name: bytes | None = None, mtime: int = 0,
+           members: bool = False):
+    """Mirror of the reference's parallel_zip(): read ifd to EOF, write one gzip member to ofd
+    (members=True: one member per batch, which the reference's own decoder reads only the first of)."""
+    o = ZipOpts(level, int(rsyncable), n_gpus, name, mtime, 0, 0, int(members))
     rc = lib().gzb_zip_fd(ifd, ofd, ctypes.byref(o))
     if rc != OK:
         raise GzbError(rc, lib().gzb_strerror(rc).decode())

@@ -1,6 +1,6 @@
 /* gzb200 -- minimal gzip-compatible front end over gzb_zip_fd(), for tests that read like the
  * reference's (tests/parallel: `gzip -j N -c < in | gzip -d | cmp`).  stdin -> stdout only.
- *   gzb200 [-1..-9] [-j NGPUS] [--rsyncable] [-N name] < in > out.gz
+ *   gzb200 [-1..-9] [-j NGPUS] [--rsyncable] [--members] [-N name] < in > out.gz
  * Option letters follow the reference's getopt table (src/gzip.c:275-315); -j here counts GPUs. */
 #include "gzb200.h"
 #include <stdio.h>
@@ -16,8 +16,9 @@ int main(int argc, char **argv)
         else if (!strcmp(a, "-j") && i + 1 < argc) o.n_gpus = atoi(argv[++i]);
         else if (!strcmp(a, "--rsyncable")) o.rsyncable = 1;
         else if (!strcmp(a, "-N") && i + 1 < argc) o.name = argv[++i];
+        else if (!strcmp(a, "--members")) o.members = 1;
         else if (!strcmp(a, "-c")) {}
-        else { fprintf(stderr, "usage: gzb200 [-1..-9] [-j NGPUS] [--rsyncable] [-N name] < in > out.gz\n"); return 2; }
+        else { fprintf(stderr, "usage: gzb200 [-1..-9] [-j NGPUS] [--rsyncable] [--members] [-N name] < in > out.gz\n"); return 2; }
     }
     if (o.n_gpus < 1) { fprintf(stderr, "gzb200: invalid number of GPUs\n"); return 2; }
     int rc = gzb_zip_fd(0, 1, &o);

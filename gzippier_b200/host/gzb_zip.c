@@ -16,6 +16,8 @@
  *
  * Batches are independent given their dictionary, so with n_gpus > 1 consecutive batches simply
  * go to different GPUs: contiguous shards on chunk boundaries, no collective.
+ * With opts->members every batch is closed as a gzip member of its own (no dictionary across batches): the
+ * "per-GPU members concatenated" layout, which the reference's own decoder reads only the first member of.
  * Differences by design: errors are reported, empty input yields the valid
  * 20-byte member instead of a deadlock (F4), and FNAME is the caller's choice (F5).
  */
@@ -150,7 +152,7 @@ static void *worker(void *arg)
         pthread_mutex_unlock(&p->mu);
         if (stop) return NULL;
         const uint8_t *data = s->in + GZB_DICT;
-        int rc = gzb_deflate_host(p->ctx[w], p->level, p->flags | (final ? GZB_F_FINAL : 0u), data, s->n,
+        int rc = gzb_deflate_host(p->ctx[w], p->level, p->flags | ((final || p->o->members) ? GZB_F_FINAL : 0u), data, s->n,
                                   (p->dict_sz && s->have_dict) ? data - p->dict_sz : NULL, s->out, p->out_cap, &s->res);
         if (rc != GZB_OK) { fail(p, rc); return NULL; }
         pthread_mutex_lock(&p->mu);
@@ -171,7 +173,19 @@ static void *writer(void *arg)
         const int stop = p->rc != GZB_OK;
         pthread_mutex_unlock(&p->mu);
         if (stop) return NULL;
+        if (p->o->members && i > 0) {             /* a member per batch: its own header (no name) ... */
+            uint8_t h[16];
+            const int hn = gzb_gzip_header(p->level, p->o->mtime, NULL, h, sizeof(h));
+            if (hn < 0 || writen(p->ofd, h, (size_t)hn)) { fail(p, GZB_E_IO); return NULL; }
+            p->o->bytes_out += (uint64_t)hn;
+        }
         if (writen(p->ofd, s->out, s->res.out_bytes)) { fail(p, GZB_E_IO); return NULL; }
+        if (p->o->members) {                      /* ... and its own trailer */
+            uint8_t tr[8];
+            gzb_gzip_trailer(s->res.crc32, s->n, tr, sizeof(tr));
+            if (writen(p->ofd, tr, 8)) { fail(p, GZB_E_IO); return NULL; }
+            p->o->bytes_out += 8;
+        }
         p->crc = gzb_crc32_combine(p->crc, s->res.crc32, s->n);
         p->o->bytes_in += s->n; p->o->bytes_out += s->res.out_bytes;
         const int final = s->final;
@@ -284,7 +298,7 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
             break;
         }
         s->n = (uint64_t)got; s->have_dict = 0;
-        if (i > 0 && p->dict_sz) {                /* the dictionary of a batch: the tail of the one before (which was full) */
+        if (i > 0 && p->dict_sz && !o->members) { /* the dictionary of a batch: the tail of the one before (which was full) */
             const slot *prev = &p->s[(i - 1) % (uint64_t)p->nslots];
             memcpy(s->in + GZB_DICT - p->dict_sz, prev->in + GZB_DICT + prev->n - p->dict_sz, p->dict_sz);
             s->have_dict = 1;
@@ -303,7 +317,7 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     for (int w = 0; w < nth; w++) pthread_join(th[w], NULL);
     if (have_writer) pthread_join(wth, NULL);
     rc = p->rc;
-    if (rc == GZB_OK) {
+    if (rc == GZB_OK && !o->members) {
         uint8_t tr[8];
         gzb_gzip_trailer(p->crc, o->bytes_in, tr, sizeof(tr));
         if (writen(ofd, tr, 8)) rc = GZB_E_IO; else o->bytes_out += 8;

@@ -148,6 +148,11 @@ typedef struct gzb_zip_opts {
     const char *name;       /* `ifname` when input is a file, else NULL (src/parallel.c:496-507) */
     uint32_t mtime;         /* `time_stamp.tv_sec`           */
     uint64_t bytes_in, bytes_out;   /* filled on return (reference globals bytes_in/bytes_out) */
+    int members;            /* 0: ONE member, fragments of all batches joined (the reference's layout, what its own
+                             * `gzip -d` reads).  1: every batch a member of its own, no dictionary across batches
+                             * ("per-GPU members concatenated"): legal RFC 1952 that gunzip, zlib's gzread and Python's
+                             * gzip decode in full, but the reference's decoder stops after the first member
+                             * (src/unzip.c:361, src/gzip.c:1024-1030) -- hence off by default. */
 } gzb_zip_opts;
 int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *opts);
 

@@ -253,6 +253,37 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
         assert e.value.code == gz.E_IO
 
 
+def test_zip_fd_member_per_batch(gz, orc, tmp_path, monkeypatch):
+    """opts.members (BASELINE config 5's "per-GPU members concatenated"): every batch a complete member.
+    Multi-member decoders restore the whole input; each member is what a one-shot call on that batch gives; and the
+    reference's own decoder, which reads only the first member (src/unzip.c:361), returns exactly the first batch."""
+    import gzip, io
+    B = 4 << 20
+    n = 40 * (1 << 20) + 999                     # above the small-input threshold: 10 full batches and a short one
+    d = gz.corpus("text", n, seed=5)
+    src = tmp_path / "in.bin"; src.write_bytes(d.tobytes())
+    monkeypatch.setenv("GZB_ZIP_BATCH_MB", "4")
+    dst = tmp_path / "out.gz"
+    with open(src, "rb") as fi, open(dst, "wb") as fo:
+        bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=6, members=True)
+    m = dst.read_bytes()
+    assert bi == n and bo == len(m)
+    assert gzip.GzipFile(fileobj=io.BytesIO(m)).read() == d.tobytes()                                       # Python gzip
+    assert subprocess.run(["gunzip", "-c"], input=m, stdout=subprocess.PIPE, check=True).stdout == d.tobytes()  # system gunzip
+    # member by member
+    off, k = 0, 0
+    while off < len(m):
+        part = d[k * B:(k + 1) * B]
+        body = orc.engine_model(part, 6).tobytes()
+        assert m[off:off + 10] == gz.gzip_header(6)
+        assert m[off + 10:off + 10 + len(body)] == body
+        assert m[off + 10 + len(body):off + 18 + len(body)] == gz.gzip_trailer(zlib.crc32(part.tobytes()), len(part))
+        off += 18 + len(body); k += 1
+    assert off == len(m) and k == 11
+    if orc.have_ref():
+        assert orc.ref_gunzip(m) == d[:B].tobytes()
+
+
 def test_device_side_verify(gz, orc, ctx, monkeypatch):
     """GZB_F_VERIFY: every fragment is decoded again on the device and compared with the input.  It must
     pass on good output of every kind of block and catch a single corrupted byte anywhere."""
