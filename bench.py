@@ -211,14 +211,14 @@ def main():
         traffic = prof["dram_bytes_per_input_byte"] * n / nsub
     except (OSError, KeyError, ValueError):
         pass
-    cpu = None if a.no_cpu_baseline else pick_cpu_sample(a.level, a.corpus, threads)
+    cpu = None if (a.no_cpu_baseline or world > 1) else pick_cpu_sample(a.level, a.corpus, threads)   # rank 0 at N=1 only
     line = {"metric": "compress input GB/s", "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": round(ms / a.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": workload, "level": a.level, "chunk": gz.CHUNK, "dict": gz.DICT, "in_bytes_per_gpu": n, "out_bytes_rank0": out_bytes,
                        "ratio": round(n / out_bytes, 4), "l2": "inputs (4 GiB) larger than L2 (126 MB): no flush needed",
                        "stage_ms_per_step": {k: round(v / a.steps, 3) for k, v in stage.items()}},
             "e2e": {"value": round(e2e, 3), "unit": "GB/s", "h2d_bytes_per_step": n + halo, "d2h_bytes_per_step": int(out_bytes), "steps": e2e_steps},
-            "gpu_launches": a.steps * nsub * 5,
+            "gpu_launches": world * a.steps * nsub * 5,                    # five kernels per sub-batch of 4096 chunks, on every rank
             "roofline": {"bound": "hbm", "kernel": "k_lz77", "achieved": round(achieved, 3), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5),
                          "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                          "note": "integer/latency-bound path: the HBM fraction is small by construction (SURVEY 8d); see profiles/ for issue-slot utilisation"},
