@@ -96,7 +96,10 @@ uint64_t gzb_bound(uint64_t n, uint32_t flags);
  * d_in and d_out must be 16-byte aligned.  Replaces the per-job body of
  * compress_thread (src/parallel.c:595-688: deflateReset/Params/SetDictionary/
  * deflate/crc32z).  Runs on `stream` (a cudaStream_t, or NULL for the
- * context's own stream) and returns after the result is known. */
+ * context's own stream) and returns after the result is known.  The context's
+ * own stream is non-blocking: it is NOT ordered with the legacy default stream,
+ * so a caller that fills d_in or reads d_out on another stream passes that
+ * stream here or synchronises itself. */
 int gzb_deflate_device(gzb_ctx *ctx, int level, uint32_t flags,
                        const uint8_t *d_in, uint64_t n, uint32_t halo,
                        uint8_t *d_out, uint64_t out_cap,

@@ -18,3 +18,29 @@ for level in range(1, 10):
         if not same: bad += 1
     print(f"L{level} {kind}: {n} -> {r0.out_bytes}, {reps} repetitions identical: {bad == 0}", flush=True)
 print("bad:", bad)
+
+# second phase: two contexts on two host threads at once (their kernels share the SMs, so every CTA sees different
+# neighbours and timing than alone); the bytes must still be those of the runs above
+import threading
+ref = {}
+for level in (1, 4, 6, 9):
+    r = ctx.deflate_device(t_in, n, outs[0], level, flags=gz.F_FINAL)
+    ref[level] = (r.out_bytes, r.crc32, outs[0][: r.out_bytes].clone())
+    torch.cuda.synchronize()            # the clone runs on torch's stream, the next call on the context's: order them
+def hammer(dev_out, levels, res):
+    c = gz.Context(0)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        for level in levels:
+            r = c.deflate_device(t_in, n, dev_out, level, flags=gz.F_FINAL | gz.F_VERIFY, stream=s.cuda_stream)
+            ob, crc, want = ref[level]
+            if not (r.out_bytes == ob and r.crc32 == crc and bool(torch.equal(dev_out[:ob], want))):
+                res.append(level)
+                if os.environ.get("STRESS_DEBUG"):
+                    m = min(ob, r.out_bytes); diff = (dev_out[:m] != want[:m]).nonzero()
+                    print("  mismatch L%d: out %d vs %d, crc same %s, differing bytes %d, first at %s" % (level, r.out_bytes, ob, r.crc32 == crc, diff.numel(), int(diff[0]) if diff.numel() else None), flush=True)
+res = []
+ta = threading.Thread(target=hammer, args=(outs[0], [6, 1, 9, 4] * reps, res)); tb = threading.Thread(target=hammer, args=(outs[1], [9, 6, 4, 1] * reps, res))
+ta.start(); tb.start(); ta.join(); tb.join()
+print("concurrent contexts: mismatches", res)
+print("bad (total):", bad + len(res))
