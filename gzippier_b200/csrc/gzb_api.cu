@@ -236,6 +236,8 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     lp.parse_warps = getenv("GZB_PW") ? atoi(getenv("GZB_PW")) : (level <= 3 ? 16 : 8);
     lp.flow = getenv("GZB_FLOW") ? atoi(getenv("GZB_FLOW")) : (level >= 7 ? 2 : level >= 5 ? 1 : 0);
     lp.spin_ns = getenv("GZB_SPIN") ? atoi(getenv("GZB_SPIN")) : 100;
+    // warp roles: measured on B200 (tools/variant_sweep.py, profiles/r01f_variant_sweep.txt)
+    lz77_role_map(lp, getenv("GZB_ROLEMAP") ? atoi(getenv("GZB_ROLEMAP")) : (lp.flow && lp.parse_warps == 8 ? 11 : 0));
     ctx->n_sub_timed = 0;
 
     CU(ctx, cudaMemsetAsync(ctx->d_cursor, 0, sizeof(Cursor), st));

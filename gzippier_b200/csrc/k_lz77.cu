@@ -118,23 +118,45 @@ __device__ __forceinline__ int match_len_s(uint32_t ring_s, uint32_t p, uint32_t
 
 // Copy stream bytes [t*TILE, (t+1)*TILE) into the ring, zero beyond the end of the stream.
 // nthr threads of the caller cooperate (tid in [0, nthr)), 16 bytes per thread per step.
+__device__ __forceinline__ uint4 tile_fetch(const uint8_t* sp, uint32_t n_s, uint32_t pos)
+{
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (pos + 16u <= n_s) v = __ldg(reinterpret_cast<const uint4*>(sp + pos));
+    else if (pos < n_s) {
+        uint32_t w[4] = {0, 0, 0, 0};
+        for (uint32_t k = 0; pos + k < n_s; k++) w[k >> 2] |= (uint32_t)sp[pos + k] << ((k & 3u) * 8u);
+        v = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    return v;
+}
+__device__ __forceinline__ void tile_store(Smem& S, uint32_t pos, uint4 v)
+{
+    const uint32_t ra = pos & 0xFFFFu;
+    *reinterpret_cast<uint4*>(&S.ring32[ra >> 2]) = v;
+    if (ra < (uint32_t)RING_MIRROR) *reinterpret_cast<uint4*>(&S.ring32[(RING + ra) >> 2]) = v;
+}
 __device__ __forceinline__ void load_tile(Smem& S, const uint8_t* sp, uint32_t n_s, uint32_t t, uint32_t tid, uint32_t nthr)
 {
     uint32_t base = t * TILE;
-    for (uint32_t o = tid * 16u; o < TILE; o += nthr * 16u) {
-        uint32_t pos = base + o;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (pos + 16u <= n_s) v = __ldg(reinterpret_cast<const uint4*>(sp + pos));
-        else if (pos < n_s) {
-            uint32_t w[4] = {0, 0, 0, 0};
-            for (uint32_t k = 0; pos + k < n_s; k++) w[k >> 2] |= (uint32_t)sp[pos + k] << ((k & 3u) * 8u);
-            v = make_uint4(w[0], w[1], w[2], w[3]);
-        }
+    for (uint32_t o = tid * 16u; o < TILE; o += nthr * 16u) tile_store(S, base + o, tile_fetch(sp, n_s, base + o));
+}
+
+// The same copy with cp.async: no registers, no waiting -- issued before a warp's own work, awaited after it.
+__device__ __forceinline__ void load_tile_async(uint32_t sbase, const uint8_t* sp, uint32_t n_s, uint32_t t, uint32_t lane)
+{
+    const uint32_t ring_s = sbase + (uint32_t)offsetof(Smem, ring32);
+#pragma unroll
+    for (uint32_t j = 0; j < (uint32_t)TILE / 512u; j++) {
+        const uint32_t pos = t * TILE + (j * 32u + lane) * 16u;
+        const uint32_t nb = pos < n_s ? min(16u, n_s - pos) : 0u;            // bytes past the end are zero-filled
+        const uint8_t* src = sp + (nb ? pos : 0u);
         const uint32_t ra = pos & 0xFFFFu;
-        *reinterpret_cast<uint4*>(&S.ring32[ra >> 2]) = v;
-        if (ra < (uint32_t)RING_MIRROR) *reinterpret_cast<uint4*>(&S.ring32[(RING + ra) >> 2]) = v;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" :: "r"(ring_s + ra), "l"(src), "r"(nb) : "memory");
+        if (ra < (uint32_t)RING_MIRROR)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" :: "r"(ring_s + (uint32_t)RING + ra), "l"(src), "r"(nb) : "memory");
     }
 }
+__device__ __forceinline__ void load_tile_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // ---- insertion ---------------------------------------------------------------------------------------
 // Inserting a tile into a hash table is serial per bucket, and one warp doing 64 steps of 32 positions is
@@ -390,18 +412,8 @@ __device__ __forceinline__ uint32_t parse_step(const Smem& S, const LevelParams&
 // ---- parse + emission of one tile, by the parser group (warps 0..PARSE_WARPS-1, named barrier 1) -------
 // PARSE_WARPS (8 or 16) is a template parameter of the kernel: the cheap searches of the low levels finish long before an
 // 8-warp parser does, the deep ones want the warps for searching.
-// Roles by warp.  A warp's scheduler (SMSP) is warp & 3: the three serial inserters and the loader sit together on
-// SMSP 3 with four of the parser warps (which mostly wait at their group barrier), so that the latency-bound
-// inserters get issue slots that eight search warps per scheduler would otherwise take.
+// Roles by warp: LevelParams::role, filled in by lz77_role_map() below.
 enum { ROLE_INS0 = 0, ROLE_INS1 = 1, ROLE_INS2 = 2, ROLE_LOAD = 3, ROLE_SEARCH = 4, ROLE_PARSE0 = 8 };
-template <int PARSE_WARPS>
-__device__ __forceinline__ int role_of(uint32_t warp)
-{
-    const uint32_t sm = warp & 3u, q = warp >> 2;
-    if (sm == 3u) return q < 4u ? (int)q : ROLE_PARSE0 + (int)(q - 4u);
-    if (PARSE_WARPS == 8) return (sm == 2u && q >= 4u) ? ROLE_PARSE0 + 4 + (int)(q - 4u) : ROLE_SEARCH;
-    return q >= 4u ? ROLE_PARSE0 + 4 + (int)(sm * 4u + q - 4u) : ROLE_SEARCH;
-}
 
 template <int PG> __device__ __forceinline__ void group_sync_n() { asm volatile("bar.sync 1, %0;" :: "n"(PG) : "memory"); }
 __device__ __forceinline__ void flush_block(Smem& S, BlockRec* brec, uint32_t in_end, uint32_t tid, uint32_t nthr)
@@ -601,7 +613,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     const uint32_t nruns = (nchunks + run - 1) / run;
-    const int role = role_of<PARSE_WARPS>(warp);
+    const unsigned long long role_w = warp < 8u ? lp.role_b0 : warp < 16u ? lp.role_b1 : warp < 24u ? lp.role_b2 : lp.role_b3;
+    const int role = (int)((role_w >> ((warp & 7u) * 8u)) & 0xFFu);              // lz77_role_map
 
     for (;;) {
         __syncthreads();
@@ -641,8 +654,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             // inserted), parsed (the tile whose mlen/mdist slots they are about to rewrite has been parsed) and b1_done (the
             // previous use of the barrier they are about to arrive at is over).  The barrier section -- parking the buckets
             // of tile k+2, ageing the tables -- is the role warps' business (named barrier 4).
-            constexpr uint32_t NRT = (4u + (uint32_t)PARSE_WARPS) * 32u;
-            const uint32_t rtid = (uint32_t)(role < 4 ? role : 4 + (role - ROLE_PARSE0)) * 32u + lane;
+            const uint32_t NRT = (uint32_t)__popc(lp.role_mask) * 32u;                          // threads of the role warps
+            const uint32_t rtid = (uint32_t)__popc(lp.role_mask & ((1u << warp) - 1u)) * 32u + lane;
             for (int k = -1; k <= (int)ntiles; k++) {
                 const bool do_insert = k + 1 < (int)ntiles;
                 const bool do_hash = k + 2 < (int)ntiles;
@@ -669,6 +682,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     bar_arrive_n(b1, LZ_THREADS);
                 } else {
                     if (role <= ROLE_INS2) {
+                        const bool loads = role == ROLE_INS0 && lp.ins0_loads;
+                        if (loads) load_tile_async(sbase, sp, n_s, (uint32_t)(k + 3), lane);
                         if (do_insert) {
                             long long c0 = clock64();
                             const uint32_t t = (uint32_t)(k + 1);
@@ -679,6 +694,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                             __syncwarp();
                             if (lane == 0) { __threadfence_block(); atomicAdd(&S.ins_total, 1u); }
                         }
+                        if (loads) load_tile_wait();
                     } else if (role == ROLE_LOAD) {
                         load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);
                     } else if (do_parse) {
@@ -713,6 +729,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             // roles: three serial inserter warps (raw heads), one loader, eight parser warps; everybody else -- and
             // everybody who is done -- searches
             if (role <= ROLE_INS2) {
+                const bool loads = role == ROLE_INS0 && lp.ins0_loads;
+                if (loads) load_tile_async(sbase, sp, n_s, (uint32_t)(k + 3), lane);
                 if (do_insert) {
                     long long c0 = clock64();
                     const uint32_t t = (uint32_t)(k + 1);
@@ -721,6 +739,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                     else insert_tile<2, false>(S, sbase, t, n_s, lane);
                     pf[6] += (unsigned long long)(clock64() - c0);
                 }
+                if (loads) load_tile_wait();
             } else if (role == ROLE_LOAD) {
                 load_tile(S, sp, n_s, (uint32_t)(k + 3), lane, 32);   // zero-fills past the end of the stream
             } else if (do_parse && role >= ROLE_PARSE0) {
@@ -787,6 +806,36 @@ cudaError_t lz77_configure()
     e = cudaFuncSetAttribute(k_lz77<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_lz77<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+}
+
+// Roles by warp.  A warp's scheduler (SMSP) is warp & 3.  preset = layout + 10 * loader:
+//   layout 0: the three serial inserters sit together on SMSP 3 with four of the parser warps (which mostly wait at
+//             their group barrier), so that the latency-bound inserters get issue slots that eight search warps per
+//             scheduler would otherwise take; the other parsers on SMSP 2 (8) or everywhere (16)
+//   layout 1: the 8 parsers two per scheduler: 6 / 6 / 6 / 3 search warps instead of 8 / 8 / 4 / 1
+//   loader 0: a loader warp (warp 15) brings tile k+3 into the ring
+//   loader 1: no loader warp (one more search warp, on the scheduler with the most free issue slots): the 6-byte
+//             inserter issues the copy as cp.async before it inserts and waits for it afterwards
+void lz77_role_map(LevelParams& lp, int preset)
+{
+    const int pw = lp.parse_warps, layout = preset % 10;
+    int np = 0;
+    lp.ins0_loads = preset / 10;
+    unsigned long long b[4] = {0, 0, 0, 0};
+    lp.role_mask = 0;
+    for (int w = 0; w < 32; w++) {
+        const int sm = w & 3, q = w >> 2;
+        int r = ROLE_SEARCH;
+        if (sm == 3 && q < 3) r = q;
+        else if (sm == 3 && q == 3) r = lp.ins0_loads ? ROLE_SEARCH : ROLE_LOAD;
+        else if (pw == 16) { if (q >= 4) r = ROLE_PARSE0; }
+        else if (layout == 1) { if (q >= 6) r = ROLE_PARSE0; }
+        else if (sm >= 2 && q >= 4) r = ROLE_PARSE0;
+        if (r == ROLE_PARSE0) r += np++;
+        b[w >> 3] |= (unsigned long long)r << ((w & 7) * 8);
+        if (r != ROLE_SEARCH) lp.role_mask |= 1u << w;
+    }
+    lp.role_b0 = b[0]; lp.role_b1 = b[1]; lp.role_b2 = b[2]; lp.role_b3 = b[3];
 }
 
 void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
