@@ -9,7 +9,7 @@
 // searched in parallel (one lane per position), and the greedy/lazy parse -- a pure function
 // next(p) of the per-position matches -- is evaluated with pointer doubling instead of a walk.
 //
-// One persistent CTA (1024 threads, ~226 KB shared memory) per SM takes runs of up to 8
+// One persistent CTA (1024 threads, ~226 KB shared memory) per SM takes runs of up to 32
 // consecutive chunks from an atomic counter and streams through them: the tables at the end of
 // a chunk ARE the next chunk's dictionary, so only the first chunk of a run inserts its 32 KiB
 // dictionary.  Per tile k the CTA runs three things at once (one barrier per tile):
@@ -176,22 +176,40 @@ __device__ __forceinline__ uint32_t bucket_of(uint32_t v, uint32_t v2)
     return KIND == 0 ? hash6(v, v2 & 0xFFFFu) : KIND == 1 ? hash3(v) : hash4(v);
 }
 
-__device__ __forceinline__ void hash_pos(Smem& S, uint32_t t, uint32_t o)
+// N (2 or 4) consecutive positions per thread, o0 a multiple of N: three ring words cover the N + 7 bytes they need, and
+// the N buckets of a table go out as one store.
+template <int N>
+__device__ __forceinline__ void hash_span(Smem& S, uint32_t t, uint32_t o0)
 {
     // the bucket of a position is parked where its link / c3 / c4 entry will go: those slots are dead until insertion
-    const uint32_t p = t * TILE + o;
-    const uint32_t v = ring_ld32(S.ring32, p), v2 = ring_ld32(S.ring32, p + 4u);      // zero past the end of the stream
-    uint32_t slot = (t * TILE) % LINK_RING + o; if (slot >= LINK_RING) slot -= LINK_RING;
-    S.link[slot] = (uint16_t)bucket_of<0>(v, v2); S.c3[t & 1][o] = (uint16_t)bucket_of<1>(v, v2); S.c4[t & 1][o] = (uint16_t)bucket_of<2>(v, v2);
+    static_assert(N == 2 || N == 4, "hash_span");
+    const uint32_t a = (t * TILE + o0) & 0xFFFFu, i = a >> 2, sh = (a & 3u) * 8u;     // sh = 0 (N == 4), 0 or 16 (N == 2)
+    const uint32_t w0 = S.ring32[i], w1 = S.ring32[i + 1], w2 = S.ring32[i + 2];      // may be the mirror; zero past the end of the stream
+    uint32_t b6[N], b3[N], b4[N];
+#pragma unroll
+    for (int j = 0; j < N; j++) {
+        const uint32_t v = __funnelshift_r(w0, w1, sh + 8u * j), v2 = __funnelshift_r(w1, w2, sh + 8u * j);
+        b6[j] = bucket_of<0>(v, v2); b3[j] = bucket_of<1>(v, v2); b4[j] = bucket_of<2>(v, v2);
+    }
+    const uint32_t slot = (t * TILE) % LINK_RING + o0;                                // a tile's link slots do not wrap
+    if (N == 2) {
+        *reinterpret_cast<uint32_t*>(&S.link[slot]) = b6[0] | (b6[1] << 16);
+        *reinterpret_cast<uint32_t*>(&S.c3[t & 1][o0]) = b3[0] | (b3[1] << 16);
+        *reinterpret_cast<uint32_t*>(&S.c4[t & 1][o0]) = b4[0] | (b4[1] << 16);
+    } else {
+        *reinterpret_cast<uint2*>(&S.link[slot]) = make_uint2(b6[0] | (b6[1] << 16), b6[2] | (b6[3] << 16));
+        *reinterpret_cast<uint2*>(&S.c3[t & 1][o0]) = make_uint2(b3[0] | (b3[1] << 16), b3[2] | (b3[3] << 16));
+        *reinterpret_cast<uint2*>(&S.c4[t & 1][o0]) = make_uint2(b4[0] | (b4[1] << 16), b4[2] | (b4[3] << 16));
+    }
 }
 __device__ void hash_tile_n(Smem& S, uint32_t t, uint32_t idx, uint32_t nthr)
 {
-    for (uint32_t o = idx; o < (uint32_t)TILE; o += nthr) hash_pos(S, t, o);
+    for (uint32_t q = idx; q < (uint32_t)TILE / 4u; q += nthr) hash_span<4>(S, t, q * 4u);
 }
 __device__ void hash_tile(Smem& S, uint32_t t, uint32_t tid)
 {
-#pragma unroll
-    for (int j = 0; j < TILE / LZ_THREADS; j++) hash_pos(S, t, tid + (uint32_t)j * LZ_THREADS);
+    static_assert(TILE == 2 * LZ_THREADS, "hash_tile: one pair of positions per thread");
+    hash_span<2>(S, t, tid * 2u);
 }
 
 // One step = 32 consecutive positions, lane = position.  The loop is written on shared-space addresses and kept as
@@ -842,12 +860,12 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st)
 {
     if (nchunks == 0) return;
-    // chunks per run: up to 8, whichever keeps the SMs busiest; independent chunks (--rsyncable: no dictionary) are
+    // chunks per run: up to 32, whichever keeps the SMs busiest; independent chunks (--rsyncable: no dictionary) are
     // never chained
     // (cost of a choice: waves of runs over the SMs x tiles per run; the 16 dictionary tiles of a run are inserted
     // but neither searched nor parsed, which makes them about as dear as 10 full ones)
     uint32_t run = 1;
-    const int max_run = getenv("GZB_MAX_RUN") ? atoi(getenv("GZB_MAX_RUN")) : 8;
+    const int max_run = getenv("GZB_MAX_RUN") ? atoi(getenv("GZB_MAX_RUN")) : 32;
     if (dict) {
         uint64_t best_cost = ~0ull;
         for (uint32_t r = 1; r <= (uint32_t)max_run; r++) {
@@ -856,6 +874,7 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
             if (cost < best_cost) { best_cost = cost; run = r; }
         }
     }
+    if (dict && getenv("GZB_FORCE_RUN") && atoi(getenv("GZB_FORCE_RUN")) > 0) run = (uint32_t)atoi(getenv("GZB_FORCE_RUN"));   // tests
     const uint32_t nruns = (nchunks + run - 1) / run;
     const uint32_t grid = nruns < (uint32_t)n_sm ? nruns : (uint32_t)n_sm;
     if (lp.parse_warps == 16) k_lz77<16, false><<<grid, LZ_THREADS, sizeof(Smem), st>>>(in, n_bytes, halo, chunk, dict, nchunks, run, tokens, blocks, chunks, lp, work_ctr);

@@ -208,11 +208,17 @@ def test_kernel_variants_give_the_same_bytes(gz, orc, ctx, monkeypatch, pw, flow
         for level in (1, 4, 6, 9):
             raw, r = ctx.deflate_host(d, level)
             assert raw.tobytes() == orc.engine_model(d, level).tobytes(), (kind, level)
-    # long runs of chained chunks (up to 8 per CTA) at full occupancy
+    # runs of chained chunks at full occupancy (the launch picks the run length: 5 here)
     d = gz.corpus("text", 700 * gz.CHUNK + 99, seed=6)
     raw, r = ctx.deflate_host(d, 6)
     assert r.crc32 == zlib.crc32(d.tobytes()) and zlib.decompress(raw.tobytes(), -15) == d.tobytes()
-    assert raw.tobytes() == orc.engine_model(d, 6).tobytes()
+    want = orc.engine_model(d, 6).tobytes()
+    assert raw.tobytes() == want
+    # the longest runs a launch ever picks (32 chunks per CTA, what a 4 GiB call uses), and odd ones
+    for run in ("32", "13"):
+        monkeypatch.setenv("GZB_FORCE_RUN", run)
+        raw, r = ctx.deflate_host(d, 6)
+        assert raw.tobytes() == want, run
 
 
 def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):

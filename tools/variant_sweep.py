@@ -8,11 +8,11 @@ kind = sys.argv[2] if len(sys.argv) > 2 else "text"
 levels = [int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 else [6]
 ctx = gz.Context(0)
 d = gz.corpus(kind, n); t_in = torch.from_numpy(d).cuda(); t_out = torch.empty(gz.bound(n), dtype=torch.uint8, device="cuda")
-variants = [dict(GZB_ROLEMAP=r) for r in (0, 1, 10, 11)]
+variants = [dict()]
 for level in levels:
     ref = None
     for v in variants:
-        for k in ("GZB_ROLEMAP", "GZB_SPIN", "GZB_FLOW"): os.environ.pop(k, None)
+        for k in ("GZB_ROLEMAP", "GZB_SPIN", "GZB_FLOW", "GZB_MAX_RUN"): os.environ.pop(k, None)
         for k, x in v.items(): os.environ[k] = str(x)
         best = 1e9
         for _ in range(3):
