@@ -831,6 +831,7 @@ cudaError_t lz77_configure()
 //             their group barrier), so that the latency-bound inserters get issue slots that eight search warps per
 //             scheduler would otherwise take; the other parsers on SMSP 2 (8) or everywhere (16)
 //   layout 1: the 8 parsers two per scheduler: 6 / 6 / 6 / 3 search warps instead of 8 / 8 / 4 / 1
+//   layout 2, 3: the inserters' scheduler holds 5 (4) parsers and no (one) search warp: 7 / 7 / 7 / 0 (7 / 7 / 6 / 1)
 //   loader 0: a loader warp (warp 15) brings tile k+3 into the ring
 //   loader 1: no loader warp (one more search warp, on the scheduler with the most free issue slots): the 6-byte
 //             inserter issues the copy as cp.async before it inserts and waits for it afterwards
@@ -838,16 +839,18 @@ void lz77_role_map(LevelParams& lp, int preset)
 {
     const int pw = lp.parse_warps, layout = preset % 10;
     int np = 0;
-    lp.ins0_loads = preset / 10;
+    lp.ins0_loads = (preset / 10 || layout == 2) ? 1 : 0;           // layout 2 has no room for a loader warp
     unsigned long long b[4] = {0, 0, 0, 0};
     lp.role_mask = 0;
     for (int w = 0; w < 32; w++) {
         const int sm = w & 3, q = w >> 2;
         int r = ROLE_SEARCH;
         if (sm == 3 && q < 3) r = q;
-        else if (sm == 3 && q == 3) r = lp.ins0_loads ? ROLE_SEARCH : ROLE_LOAD;
+        else if (sm == 3 && q == 3 && (layout != 2 || !lp.ins0_loads)) r = lp.ins0_loads ? ROLE_SEARCH : ROLE_LOAD;
         else if (pw == 16) { if (q >= 4) r = ROLE_PARSE0; }
         else if (layout == 1) { if (q >= 6) r = ROLE_PARSE0; }
+        else if (layout == 2) { if (sm == 3 ? q >= 3 : q >= 7) r = ROLE_PARSE0; }                 // 7 / 7 / 7 / 0
+        else if (layout == 3) { if (sm == 3 ? q >= 4 : sm == 2 ? q >= 6 : q >= 7) r = ROLE_PARSE0; } // 7 / 7 / 6 / 1
         else if (sm >= 2 && q >= 4) r = ROLE_PARSE0;
         if (r == ROLE_PARSE0) r += np++;
         b[w >> 3] |= (unsigned long long)r << ((w & 7) * 8);
