@@ -50,6 +50,21 @@ __device__ void warp_sort512(uint32_t* key, uint32_t lane)
     }
 }
 
+// 32 keys, one per lane, in registers
+__device__ __forceinline__ uint32_t warp_sort32(uint32_t key, uint32_t lane)
+{
+#pragma unroll
+    for (uint32_t k = 2; k <= 32u; k <<= 1) {
+#pragma unroll
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            const uint32_t other = __shfl_xor_sync(FULL, key, (int)j);
+            const bool up = (lane & k) == 0u, lower = (lane & j) == 0u;
+            key = (lower == up) ? min(key, other) : max(key, other);
+        }
+    }
+    return key;
+}
+
 // In-place minimum-redundancy code lengths (Moffat & Katajainen); A sorted ascending.
 __device__ void min_redundancy(uint32_t* A, int n)
 {
@@ -72,26 +87,34 @@ __device__ void min_redundancy(uint32_t* A, int n)
 }
 
 // freq[0..nsym) -> lens[0..nsym) limited to maxbits; forces >= 2 coded symbols (trees.c:646-651).
-// Whole warp calls; returns the highest coded symbol.
+// Whole warp calls; returns the highest coded symbol.  SMALL: nsym <= 32 (sorted in registers).
+template <bool SMALL>
 __device__ int huff_lengths(HuffSmem& S, const uint32_t* freq_in, int nsym, int maxbits, uint8_t* lens, uint32_t lane)
 {
     uint32_t* freq = S.ftmp;
-    for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) freq[i] = freq_in[i];
+    int used = 0;
+    for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) { const uint32_t f = freq_in[i]; freq[i] = f; used += f != 0u; }
+    for (int o = 16; o > 0; o >>= 1) used += __shfl_xor_sync(FULL, used, o);
     __syncwarp();
-    if (lane == 0) {
-        int used = 0;
-        for (int i = 0; i < nsym; i++) used += freq[i] != 0u;
+    if (used < 2 && lane == 0)
         for (int i = 0; used < 2 && i < nsym; i++) if (!freq[i]) { freq[i] = 1; used++; }
-    }
     __syncwarp();
-    for (uint32_t i = lane; i < 512u; i += 32u)
-        S.key[i] = (i < (uint32_t)nsym && freq[i]) ? ((freq[i] << 9) | i) : 0xFFFFFFFFu;
-    for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) lens[i] = 0;
-    __syncwarp();
-    warp_sort512(S.key, lane);
     int n = 0;
-    for (uint32_t i = lane; i < 512u; i += 32u) n += S.key[i] != 0xFFFFFFFFu;
-    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(FULL, n, o);
+    if (SMALL) {
+        const uint32_t key = (lane < (uint32_t)nsym && freq[lane]) ? ((freq[lane] << 9) | lane) : 0xFFFFFFFFu;
+        if (lane < (uint32_t)nsym) lens[lane] = 0;
+        S.key[lane] = warp_sort32(key, lane);
+        n = __popc(__ballot_sync(FULL, key != 0xFFFFFFFFu));
+        __syncwarp();
+    } else {
+        for (uint32_t i = lane; i < 512u; i += 32u)
+            S.key[i] = (i < (uint32_t)nsym && freq[i]) ? ((freq[i] << 9) | i) : 0xFFFFFFFFu;
+        for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) lens[i] = 0;
+        __syncwarp();
+        warp_sort512(S.key, lane);
+        for (uint32_t i = lane; i < 512u; i += 32u) n += S.key[i] != 0xFFFFFFFFu;
+        for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(FULL, n, o);
+    }
     for (uint32_t i = lane; i < (uint32_t)n; i += 32u) S.A[i] = S.key[i] >> 9;
     __syncwarp();
     int maxsym = 0;
@@ -112,28 +135,37 @@ __device__ int huff_lengths(HuffSmem& S, const uint32_t* freq_in, int nsym, int 
         }
         int j = n;
         for (int i = 1; i <= maxbits; i++) for (int l = num[i]; l > 0; l--) lens[S.key[--j] & 511u] = (uint8_t)i;
-        for (int i = 0; i < nsym; i++) if (lens[i]) maxsym = i;
     }
-    maxsym = __shfl_sync(FULL, maxsym, 0);
     __syncwarp();
+    for (uint32_t i = lane; i < (uint32_t)nsym; i += 32u) if (lens[i]) maxsym = (int)i;      // ascending per lane
+    for (int o = 16; o > 0; o >>= 1) maxsym = max(maxsym, __shfl_xor_sync(FULL, maxsym, o));
     return maxsym;
 }
 
-// canonical codes, bit-reversed for LSB-first emission; lane 0 only
-__device__ void huff_codes(const uint8_t* lens, int nsym, int maxbits, uint16_t* codes)
+// Canonical codes, bit-reversed for LSB-first emission (gen_codes, trees.c:572-605), by the whole warp: symbol
+// c * 32 + lane sits in slot c of its lane; per code length the symbols that have it are ranked with ballots, and the
+// first code of a length follows from the count of the one before.
+template <int NCH>
+__device__ void huff_codes(const uint8_t* lens, int nsym, int maxbits, uint16_t* codes, uint32_t lane)
 {
-    int cnt[16], next[16];
-    for (int i = 0; i < 16; i++) cnt[i] = 0;
-    for (int i = 0; i < nsym; i++) cnt[lens[i]]++;
-    cnt[0] = 0;
-    int code = 0;
-    for (int b = 1; b <= maxbits; b++) { code = (code + cnt[b - 1]) << 1; next[b] = code; }
-    for (int i = 0; i < nsym; i++) {
-        int l = lens[i];
-        if (!l) { codes[i] = 0; continue; }
-        uint32_t c = (uint32_t)next[l]++;
-        codes[i] = (uint16_t)(__brev(c) >> (32 - l));
+    uint32_t len[NCH], cod[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; c++) { const uint32_t i = (uint32_t)c * 32u + lane; len[c] = i < (uint32_t)nsym ? lens[i] : 0u; cod[c] = 0; }
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t code = 0, prev_cnt = 0;
+    for (uint32_t l = 1; l <= (uint32_t)maxbits; l++) {
+        code = (code + prev_cnt) << 1;
+        uint32_t cnt = 0;
+#pragma unroll
+        for (int c = 0; c < NCH; c++) {
+            const uint32_t m = __ballot_sync(FULL, len[c] == l);
+            if (len[c] == l) cod[c] = __brev(code + cnt + (uint32_t)__popc(m & lt)) >> (32u - l);
+            cnt += (uint32_t)__popc(m);
+        }
+        prev_cnt = cnt;
     }
+#pragma unroll
+    for (int c = 0; c < NCH; c++) { const uint32_t i = (uint32_t)c * 32u + lane; if (i < (uint32_t)nsym) codes[i] = (uint16_t)cod[c]; }
 }
 
 // RLE of code lengths (scan_tree/send_tree, trees.c:703-793); lane 0 only
@@ -158,14 +190,14 @@ __device__ int rle_lengths(const uint8_t* lens, int n, uint8_t* sym, uint8_t* ex
     return k;
 }
 
-struct BitW { uint8_t* out; uint32_t bitpos; };
-__device__ __forceinline__ void putbits(BitW& w, uint32_t v, int n)
+// LSB-first bit writer: bits collect in a 64-bit accumulator and leave a byte at a time
+struct BitW { uint8_t* out; uint32_t bitpos; unsigned long long acc; uint32_t nacc; };
+__device__ __forceinline__ void putbits(BitW& w, uint32_t v, int n)     // n <= 16, v < 2^n
 {
-    for (int i = 0; i < n; i++, w.bitpos++) {
-        if ((w.bitpos & 7u) == 0u) w.out[w.bitpos >> 3] = 0;
-        w.out[w.bitpos >> 3] |= (uint8_t)(((v >> i) & 1u) << (w.bitpos & 7u));
-    }
+    w.acc |= (unsigned long long)v << w.nacc; w.nacc += (uint32_t)n; w.bitpos += (uint32_t)n;
+    while (w.nacc >= 8u) { *w.out++ = (uint8_t)w.acc; w.acc >>= 8; w.nacc -= 8u; }
 }
+__device__ __forceinline__ void flushbits(BitW& w) { if (w.nacc) { *w.out++ = (uint8_t)w.acc; w.acc = 0; w.nacc = 0; } }
 
 __device__ __forceinline__ uint32_t static_llen(uint32_t i) { return i < 144u ? 8u : i < 256u ? 9u : i < 280u ? 7u : 8u; }
 
@@ -184,8 +216,8 @@ k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, ui
     if (lane == 0) S.lfreq[256] = 1;                       // EOB (init_block, trees.c:407-420)
     __syncwarp();
 
-    int maxl = huff_lengths(S, S.lfreq, NLSYM, 15, S.llen, lane);
-    int maxd = huff_lengths(S, S.dfreq, NDSYM, 15, S.dlen, lane);
+    int maxl = huff_lengths<false>(S, S.lfreq, NLSYM, 15, S.llen, lane);
+    int maxd = huff_lengths<true>(S, S.dfreq, NDSYM, 15, S.dlen, lane);
     if (maxl < 256) maxl = 256;
     const int hlit = maxl + 1, hdist = maxd + 1;
 
@@ -200,13 +232,28 @@ k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, ui
     }
     nrle = __shfl_sync(FULL, nrle, 0);
     __syncwarp();
-    huff_lengths(S, S.bfreq, 19, 7, S.blen, lane);
+    huff_lengths<true>(S, S.bfreq, 19, 7, S.blen, lane);
+    huff_codes<1>(S.blen, 19, 7, S.bcode, lane);
+    __syncwarp();
+
+    // body sizes in bits under the dynamic and the static code (all lanes, then a warp sum)
+    unsigned long long dyn_body = 0, sta_body = 0;
+    for (uint32_t i = lane; i < (uint32_t)NLSYM; i += 32u) {
+        const uint32_t ex = i >= 257u ? len_extra_bits(i - 257u) : 0u;
+        dyn_body += (unsigned long long)S.lfreq[i] * (S.llen[i] + ex);
+        sta_body += (unsigned long long)S.lfreq[i] * (static_llen(i) + ex);
+    }
+    if (lane < (uint32_t)NDSYM) {
+        const uint32_t ex = dist_extra_bits(lane);
+        dyn_body += (unsigned long long)S.dfreq[lane] * (S.dlen[lane] + ex);
+        sta_body += (unsigned long long)S.dfreq[lane] * (5u + ex);
+    }
+    for (int o = 16; o > 0; o >>= 1) { dyn_body += __shfl_xor_sync(FULL, dyn_body, o); sta_body += __shfl_xor_sync(FULL, sta_body, o); }
 
     if (lane == 0) {
         int hclen = 19;
         while (hclen > 4 && S.blen[c_bl_order[hclen - 1]] == 0) hclen--;
-        huff_codes(S.blen, 19, 7, S.bcode);
-        BitW w = {S.header, 0};
+        BitW w = {S.header, 0, 0ull, 0};
         putbits(w, (uint32_t)(hlit - 257), 5); putbits(w, (uint32_t)(hdist - 1), 5); putbits(w, (uint32_t)(hclen - 4), 4);
         for (int i = 0; i < hclen; i++) putbits(w, S.blen[c_bl_order[i]], 3);
         for (int i = 0; i < nrle; i++) {
@@ -214,19 +261,10 @@ k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, ui
             putbits(w, S.bcode[sy], S.blen[sy]);
             if (sy == 16u) putbits(w, S.rext[i], 2); else if (sy == 17u) putbits(w, S.rext[i], 3); else if (sy == 18u) putbits(w, S.rext[i], 7);
         }
+        flushbits(w);
         const uint32_t header_bits = w.bitpos;
         // sizes in bits (header included, 3 type bits excluded)
-        unsigned long long dyn = header_bits, sta = 0;
-        for (uint32_t i = 0; i < (uint32_t)NLSYM; i++) {
-            uint32_t ex = i >= 257u ? len_extra_bits(i - 257u) : 0u;
-            dyn += (unsigned long long)S.lfreq[i] * (S.llen[i] + ex);
-            sta += (unsigned long long)S.lfreq[i] * (static_llen(i) + ex);
-        }
-        for (uint32_t i = 0; i < (uint32_t)NDSYM; i++) {
-            uint32_t ex = dist_extra_bits(i);
-            dyn += (unsigned long long)S.dfreq[i] * (S.dlen[i] + ex);
-            sta += (unsigned long long)S.dfreq[i] * (5u + ex);
-        }
+        const unsigned long long dyn = header_bits + dyn_body, sta = sta_body;
         // choice (cf. trees.c:945-993): bytes rounded up, 3 type bits included
         const uint32_t in_bytes = B->in_bytes;
         unsigned long long dyn_b = (dyn + 3 + 7) >> 3, sta_b = (sta + 3 + 7) >> 3;
@@ -247,7 +285,7 @@ k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, ui
         S.dlen[lane] = (lane < (uint32_t)NDSYM) ? 5 : 0;
         __syncwarp();
     }
-    if (lane == 0) { huff_codes(S.llen, type == 1u ? 288 : NLSYM, 15, B->lcode); huff_codes(S.dlen, NDSYM, 15, B->dcode); }
+    huff_codes<9>(S.llen, type == 1u ? 288 : NLSYM, 15, B->lcode, lane); huff_codes<1>(S.dlen, NDSYM, 15, B->dcode, lane);
     for (uint32_t i = lane; i < 288u; i += 32u) B->llen[i] = (i < (uint32_t)NLSYM || type == 1u) ? S.llen[i] : 0;
     B->dlen[lane] = (lane < (uint32_t)NDSYM) ? S.dlen[lane] : 0;
     for (uint32_t i = lane; i < (uint32_t)HDR_BYTES; i += 32u) B->header[i] = S.header[i];
