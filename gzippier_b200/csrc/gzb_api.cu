@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 #include <new>
 
 using namespace gzb;
@@ -447,8 +448,23 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     const uint64_t HOST_BATCH = (getenv("GZB_HOST_BATCH_MB") ? (uint64_t)atoi(getenv("GZB_HOST_BATCH_MB")) : 512ull) << 20;   // multiple of both chunk sizes
     std::lock_guard<std::mutex> g(ctx->mu);
     CU(ctx, cudaSetDevice(ctx->device));
+    // Batch boundaries.  The H2D copy of the first batch and the D2H copy of the last one have nothing to hide behind, so
+    // a large input starts with growing batches, ends with a small one (EDGE) and runs in HOST_BATCH pieces in between.
+    const uint64_t EDGE = (getenv("GZB_HOST_EDGE_MB") ? (uint64_t)atoi(getenv("GZB_HOST_EDGE_MB")) : 64ull) << 20;   // multiple of both chunk sizes
+    std::vector<uint64_t> boff;                                             // batch i = [boff[i], boff[i + 1])
+    boff.push_back(0);
+    if (EDGE && EDGE < HOST_BATCH && n > 4 * EDGE) {
+        // sizes EDGE, 3 EDGE, 9 EDGE ... up to HOST_BATCH (a batch's H2D copy hides behind the kernels of the one before
+        // it as long as it is at most ~3 times as large: PCIe moves ~55 GB/s, the kernels take ~18 GB/s at -6), the
+        // last batch <= EDGE
+        const uint64_t rem = n - EDGE, tail = rem % EDGE ? rem % EDGE : EDGE, end_main = n - tail;
+        uint64_t pos = 0, sz = EDGE;
+        while (pos + sz < end_main) { pos += sz; boff.push_back(pos); sz = sz * 3 < HOST_BATCH ? sz * 3 : HOST_BATCH; }
+        boff.push_back(end_main);
+    } else for (uint64_t p = HOST_BATCH; p < n; p += HOST_BATCH) boff.push_back(p);
+    boff.push_back(n);
+    const uint64_t nbatch = boff.size() - 1;
     const uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;
-    const uint64_t nbatch = n ? (n + HOST_BATCH - 1) / HOST_BATCH : 1;
     const bool pin_in = n && is_pinned(in) && (!dict || is_pinned(dict)), pin_out = is_pinned(out);
     int rc = ensure_dev(ctx, dsz + bmax + 16, gzb_bound(bmax, flags));
     if (rc == GZB_OK) rc = ensure_pinned(ctx, pin_in ? 0 : dsz + bmax + 16, pin_out ? 0 : gzb_bound(bmax, flags));
@@ -458,10 +474,10 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     uint64_t opos = 0;
     struct Pend { uint64_t bytes, opos; bool live; } pend[2] = {{0, 0, false}, {0, 0, false}};   // D2H in flight per slot
 
-    auto batch_len = [&](uint64_t i) { const uint64_t off = i * HOST_BATCH; return (n - off) < HOST_BATCH ? (n - off) : HOST_BATCH; };
+    auto batch_len = [&](uint64_t i) { return boff[i + 1] - boff[i]; };
     auto issue_h2d = [&](uint64_t i) -> int {
         const int sl = (int)(i & 1);
-        const uint64_t off = i * HOST_BATCH, nb = batch_len(i);
+        const uint64_t off = boff[i], nb = batch_len(i);
         const uint8_t* halo_src = (off == 0) ? dict : in + off - dsz;       // the 32 KiB before the batch
         const uint32_t halo = (halo_src && dsz) ? dsz : 0u;
         CU(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->e_cmp[sl], 0));        // kernels of batch i-2 have read this slot
@@ -492,7 +508,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     if ((rc = issue_h2d(0)) != GZB_OK) return rc;
     for (uint64_t i = 0; i < nbatch; i++) {
         const int sl = (int)(i & 1);
-        const uint64_t off = i * HOST_BATCH, nb = batch_len(i);
+        const uint64_t off = boff[i], nb = batch_len(i);
         const uint32_t halo = ((off == 0 ? dict != nullptr : true) && dsz) ? dsz : 0u;
         const uint32_t f = (flags & ~GZB_F_FINAL) | ((i + 1 == nbatch && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
         if ((rc = drain(sl)) != GZB_OK) return rc;                          // d_out[sl] / h_out[sl] are free again

@@ -194,6 +194,13 @@ def test_host_pipeline_batches_and_sub_batches(gz, orc, monkeypatch):
             assert raw.tobytes() == want and r.crc32 == zlib.crc32(d.tobytes()) and r.in_bytes == n
             raw, r = c.deflate_host(d, 6, gz.F_FINAL | gz.F_RSYNCABLE)
             assert raw.tobytes() == want_rs and r.crc32 == zlib.crc32(d.tobytes())
+        # a large input starts and ends with a small batch (GZB_HOST_EDGE_MB) around the full-size ones
+        n2 = 45 * gz.CHUNK + 777
+        d2 = gz.corpus("text", n2, seed=32)
+        want2 = orc.engine_model(d2, 6).tobytes()
+        monkeypatch.setenv("GZB_HOST_BATCH_MB", "2"); monkeypatch.setenv("GZB_HOST_EDGE_MB", "1")
+        raw, r = c.deflate_host(d2, 6)
+        assert raw.tobytes() == want2 and r.crc32 == zlib.crc32(d2.tobytes()) and r.in_bytes == n2
     finally:
         c.close()
 
