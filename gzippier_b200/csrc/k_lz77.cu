@@ -886,3 +886,4 @@ void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t ch
 }
 
 }  // namespace gzb
+static_assert(sizeof(gzb::Smem) <= 232448, "k_lz77: shared memory of one CTA (227 KB)");
