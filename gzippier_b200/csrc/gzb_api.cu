@@ -234,7 +234,7 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     const uint64_t nchunks64 = (n + chunk - 1) / chunk;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     LevelParams lp = level_params(level);
-    lp.parse_warps = getenv("GZB_PW") ? atoi(getenv("GZB_PW")) : (level <= 3 ? 16 : 8);
+    lp.parse_warps = getenv("GZB_PW") ? atoi(getenv("GZB_PW")) : (level <= 2 ? 16 : 8);
     lp.flow = getenv("GZB_FLOW") ? atoi(getenv("GZB_FLOW")) : (level >= 7 ? 2 : level >= 5 ? 1 : 0);
     lp.spin_ns = getenv("GZB_SPIN") ? atoi(getenv("GZB_SPIN")) : 100;
     // warp roles: measured on B200 (tools/variant_sweep.py, profiles/r01f_variant_sweep.txt)

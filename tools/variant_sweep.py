@@ -12,7 +12,7 @@ variants = [dict()]
 for level in levels:
     ref = None
     for v in variants:
-        for k in ("GZB_ROLEMAP", "GZB_SPIN", "GZB_FLOW", "GZB_MAX_RUN"): os.environ.pop(k, None)
+        for k in ("GZB_ROLEMAP", "GZB_SPIN", "GZB_FLOW", "GZB_MAX_RUN", "GZB_PW"): os.environ.pop(k, None)
         for k, x in v.items(): os.environ[k] = str(x)
         best = 1e9
         for _ in range(3):
