@@ -228,6 +228,18 @@ def test_kernel_variants_give_the_same_bytes(gz, orc, ctx, monkeypatch, pw, flow
         assert raw.tobytes() == want, run
 
 
+@pytest.mark.parametrize("preset", ["0", "1", "10", "11", "12", "13"])
+def test_warp_role_presets_give_the_same_bytes(gz, orc, ctx, monkeypatch, preset):
+    """What each warp of a k_lz77 CTA does (inserters, loader or cp.async copy by the 6-byte inserter, parsers, search) is a
+    launch parameter (lz77_role_map, GZB_ROLEMAP = layout + 10 * loader mode); scheduling only, never a byte."""
+    monkeypatch.setenv("GZB_ROLEMAP", preset)
+    for kind, n in (("text", 5 * gz.CHUNK + 777), ("mixed", 3 * gz.CHUNK + 1)):
+        d = gz.corpus(kind, n, seed=7)
+        for level in (1, 4, 6, 9):
+            raw, r = ctx.deflate_host(d, level)
+            assert raw.tobytes() == orc.engine_model(d, level).tobytes(), (kind, level)
+
+
 def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
     """gzb_zip_fd above its small-input threshold: reader / worker contexts / in-order writer over many batches, from a
     regular file (parallel pread) and from a pipe; the member must be header + the one-shot body + trailer."""
