@@ -431,6 +431,41 @@ bool is_pinned(const void* p)
 
 }  // namespace
 
+// Batch boundaries of the host path.  The H2D copy of the first batch and the D2H copy of the last one have nothing to
+// hide behind, so a large input starts with growing batches, ends with a small one (EDGE) and runs in HOST_BATCH pieces in
+// between.
+static std::vector<uint64_t> host_batch_plan(uint64_t n, uint64_t HOST_BATCH)
+{
+    const uint64_t EDGE = (getenv("GZB_HOST_EDGE_MB") ? (uint64_t)atoi(getenv("GZB_HOST_EDGE_MB")) : 64ull) << 20;   // multiple of both chunk sizes
+    std::vector<uint64_t> boff;
+    boff.push_back(0);
+    if (EDGE && EDGE < HOST_BATCH && n > 4 * EDGE) {
+        // sizes EDGE, 3 EDGE, 9 EDGE ... up to HOST_BATCH (a batch's H2D copy hides behind the kernels of the one before
+        // it as long as it is at most ~3 times as large: PCIe moves ~55 GB/s, the kernels take ~18 GB/s at -6), the
+        // last batch <= EDGE
+        const uint64_t rem = n - EDGE, tail = rem % EDGE ? rem % EDGE : EDGE, end_main = n - tail;
+        uint64_t pos = 0, sz = EDGE;
+        while (pos + sz < end_main) { pos += sz; boff.push_back(pos); sz = sz * 3 < HOST_BATCH ? sz * 3 : HOST_BATCH; }
+        boff.push_back(end_main);
+    } else for (uint64_t p = HOST_BATCH; p < n; p += HOST_BATCH) boff.push_back(p);
+    boff.push_back(n);
+    return boff;
+}
+static uint64_t host_batch_bytes()
+{
+    const uint64_t mb = getenv("GZB_HOST_BATCH_MB") ? (uint64_t)atoi(getenv("GZB_HOST_BATCH_MB")) : 512ull;
+    return (mb ? mb : 1ull) << 20;                                          // multiple of both chunk sizes
+}
+
+extern "C" int gzb_host_batch_plan(uint64_t n, uint64_t* off, int cap)
+{
+    if (!off) return GZB_E_ARG;
+    const std::vector<uint64_t> b = host_batch_plan(n, host_batch_bytes());
+    if ((size_t)cap < b.size()) return GZB_E_ARG;
+    for (size_t i = 0; i < b.size(); i++) off[i] = b[i];
+    return (int)b.size() - 1;
+}
+
 extern "C" {
 
 // Host buffers in, host buffers out.  The input is cut into batches of HOST_BATCH bytes that flow through a
@@ -445,24 +480,10 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
     const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
     const uint32_t dsz = rs ? 0u : GZB_DICT;
-    const uint64_t HOST_BATCH = (getenv("GZB_HOST_BATCH_MB") ? (uint64_t)atoi(getenv("GZB_HOST_BATCH_MB")) : 512ull) << 20;   // multiple of both chunk sizes
+    const uint64_t HOST_BATCH = host_batch_bytes();
     std::lock_guard<std::mutex> g(ctx->mu);
     CU(ctx, cudaSetDevice(ctx->device));
-    // Batch boundaries.  The H2D copy of the first batch and the D2H copy of the last one have nothing to hide behind, so
-    // a large input starts with growing batches, ends with a small one (EDGE) and runs in HOST_BATCH pieces in between.
-    const uint64_t EDGE = (getenv("GZB_HOST_EDGE_MB") ? (uint64_t)atoi(getenv("GZB_HOST_EDGE_MB")) : 64ull) << 20;   // multiple of both chunk sizes
-    std::vector<uint64_t> boff;                                             // batch i = [boff[i], boff[i + 1])
-    boff.push_back(0);
-    if (EDGE && EDGE < HOST_BATCH && n > 4 * EDGE) {
-        // sizes EDGE, 3 EDGE, 9 EDGE ... up to HOST_BATCH (a batch's H2D copy hides behind the kernels of the one before
-        // it as long as it is at most ~3 times as large: PCIe moves ~55 GB/s, the kernels take ~18 GB/s at -6), the
-        // last batch <= EDGE
-        const uint64_t rem = n - EDGE, tail = rem % EDGE ? rem % EDGE : EDGE, end_main = n - tail;
-        uint64_t pos = 0, sz = EDGE;
-        while (pos + sz < end_main) { pos += sz; boff.push_back(pos); sz = sz * 3 < HOST_BATCH ? sz * 3 : HOST_BATCH; }
-        boff.push_back(end_main);
-    } else for (uint64_t p = HOST_BATCH; p < n; p += HOST_BATCH) boff.push_back(p);
-    boff.push_back(n);
+    const std::vector<uint64_t> boff = host_batch_plan(n, HOST_BATCH);     // batch i = [boff[i], boff[i + 1])
     const uint64_t nbatch = boff.size() - 1;
     const uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;
     const bool pin_in = n && is_pinned(in) && (!dict || is_pinned(dict)), pin_out = is_pinned(out);

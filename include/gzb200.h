@@ -165,6 +165,13 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *opts);
 int gzb_host_alloc(gzb_ctx *ctx, uint64_t bytes, void **p);
 void gzb_host_free(void *p);
 
+/* How gzb_deflate_host cuts n input bytes into batches: off[0] = 0 < off[1] < ... < off[k] = n, k returned (1 for n = 0;
+ * GZB_E_ARG if cap < k + 1).  Host arithmetic only, no GPU needed.  The reader loop of the reference hands out fixed
+ * 128 KiB jobs (src/parallel.c:699-834); here a batch is what one H2D copy / kernel sequence / D2H copy handles, every
+ * boundary is a multiple of both chunk sizes, and a large input starts with batches of 64, 192 MiB ... and ends with one
+ * of <= 64 MiB so that the copies nothing can hide behind stay small (GZB_HOST_BATCH_MB, GZB_HOST_EDGE_MB). */
+int gzb_host_batch_plan(uint64_t n, uint64_t *off, int cap);
+
 /* ---- synthetic corpora for bench/tests (host only, csrc/corpus.c) ---- */
 #define GZB_CORPUS_TEXT    0
 #define GZB_CORPUS_ZIPF    1

@@ -87,3 +87,42 @@ def test_corpus_is_deterministic_and_sliceable(gz, golden):
     whole = gz.corpus("mixed", 3 << 20, seed=9)
     part = gz.corpus("mixed", 1234567, seed=9, offset=777777, threads=2)
     assert (whole[777777:777777 + 1234567] == part).all()
+
+
+def _plan(gz, n):
+    L = ctypes.CDLL(gz.LIB_PATH)
+    L.gzb_host_batch_plan.argtypes = [ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]
+    L.gzb_host_batch_plan.restype = ctypes.c_int
+    off = (ctypes.c_uint64 * 4096)()
+    k = L.gzb_host_batch_plan(n, off, 4096)
+    assert k >= 1
+    return [int(off[i]) for i in range(k + 1)]
+
+
+def test_host_batch_plan(gz, monkeypatch):
+    """gzb_deflate_host's batch boundaries (host arithmetic): they tile [0, n) in order, every inner boundary is a multiple
+    of both chunk sizes, no batch exceeds the full size, and a large input starts with growing batches (each at most 3x
+    the one before, so its H2D copy hides behind the previous batch's kernels) and ends with a small one."""
+    MB = 1 << 20
+    for batch_mb, edge_mb in ((512, 64), (2, 1), (8, 3), (512, 0), (4, 64)):
+        monkeypatch.setenv("GZB_HOST_BATCH_MB", str(batch_mb)); monkeypatch.setenv("GZB_HOST_EDGE_MB", str(edge_mb))
+        B, E = batch_mb * MB, edge_mb * MB
+        sizes = [0, 1, 131071, 131072, 131073, E, 4 * E, 4 * E + 1, 5 * E + 12345, B - 1, B, B + 1, 3 * B + 777, (4096 if batch_mb > 8 else 64) * MB,
+                 (4096 if batch_mb > 8 else 64) * MB + 4321, 7 * B + 3 * E + 99]
+        for n in sizes:
+            off = _plan(gz, n)
+            assert off[0] == 0 and off[-1] == n, (batch_mb, edge_mb, n)
+            lens = [b - a for a, b in zip(off, off[1:])]
+            assert all(l > 0 for l in lens) or n == 0
+            assert all(o % (128 * 1024) == 0 and o % (16 * 1024) == 0 for o in off[:-1])
+            assert max(lens) <= B
+            if E and E < B and n > 4 * E:
+                assert lens[0] == E and lens[-1] <= E
+                for a, b in zip(lens, lens[1:-1]): assert b <= 3 * a            # the ramp and the full-size run
+            else:
+                assert all(l == B for l in lens[:-1])
+    L = ctypes.CDLL(gz.LIB_PATH)
+    L.gzb_host_batch_plan.argtypes = [ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]
+    off = (ctypes.c_uint64 * 2)()
+    monkeypatch.setenv("GZB_HOST_BATCH_MB", "1"); monkeypatch.setenv("GZB_HOST_EDGE_MB", "0")
+    assert L.gzb_host_batch_plan(10 * MB, off, 2) == gz.E_ARG                   # needs 11 entries
