@@ -26,8 +26,23 @@ struct Scratch {
 
 }  // namespace
 
+// Scheduling knobs, read from the environment ONCE, in gzb_create (DESIGN.md "Tuning knobs").  None changes a byte of output.
+struct Tuning {
+    int pw = 0;               // GZB_PW: parser group of 8 / 16 warps (0: by level)
+    int help = -1;            // GZB_HELP: bit 0 inserters, bit 1 parsers take search groups when idle (-1: by level)
+    int rolemap = -1;         // GZB_ROLEMAP: warp layout of k_lz77 (-1: by level)
+    int max_run = 32;         // GZB_MAX_RUN
+    int force_run = 0;        // GZB_FORCE_RUN (tests)
+    uint64_t host_batch = 512ull << 20, host_edge = 64ull << 20;   // GZB_HOST_BATCH_MB, GZB_HOST_EDGE_MB
+};
+
 struct gzb_ctx {
     int device = 0, n_sm = 0;
+    Tuning tune;
+    ChunkRec* d_crc_recs = nullptr; ChunkRec* h_crc_recs = nullptr;   // gzb_crc32_device: one record per chunk, 65536 chunks per launch
+#ifdef GZB_TESTING
+    long long test_corrupt_at = -1;               // fault injection for the tests of k_verify (test build only)
+#endif
     cudaStream_t stream = nullptr;
     uint32_t* d_tab = nullptr;                    // CRC tables (CRC_TAB_WORDS words)
     uint32_t  h_x2n[64];
@@ -79,16 +94,18 @@ void build_crc_tables(uint32_t* tab /* CRC_TAB_WORDS */)
     for (int k = 1; k < 64; k++) { p = gf2_mul(p, p); tab[1024 + k] = p; }
 }
 
-const LevelParams& level_params(int level)
+LevelParams level_params(int level)
 {
     // good/lazy/nice: the reference's configuration_table (lib/zlib/deflate.c:134-146).
     // depth: candidates examined per position (every position is searched, chains keyed on 6 bytes).
-    static const LevelParams t[10] = {
-        {0, 0, 0, 0, 0, 0, 0, 0, 0},
-        {1, 8, 4, 0, 1, 1, 0, 0, 0},   {2, 16, 5, 0, 1, 1, 0, 0, 0},   {4, 32, 6, 0, 1, 1, 0, 0, 0},
-        {4, 16, 4, 1, 1, 1, 0, 0, 0},  {6, 32, 16, 1, 1, 1, 0, 0, 0},  {8, 128, 16, 1, 1, 1, 0, 0, 0},
-        {16, 128, 32, 1, 1, 1, 0, 0, 0}, {32, 258, 128, 1, 1, 1, 0, 0, 0}, {64, 258, 258, 1, 1, 1, 0, 0, 0}};
-    return t[level];
+    static const int t[10][6] = {
+        {0, 0, 0, 0, 0, 0},
+        {1, 8, 4, 0, 1, 1},   {2, 16, 5, 0, 1, 1},   {4, 32, 6, 0, 1, 1},
+        {4, 16, 4, 1, 1, 1},  {6, 32, 16, 1, 1, 1},  {8, 128, 16, 1, 1, 1},
+        {16, 128, 32, 1, 1, 1}, {32, 258, 128, 1, 1, 1}, {64, 258, 258, 1, 1, 1}};
+    LevelParams lp; memset(&lp, 0, sizeof(lp));
+    lp.depth = t[level][0]; lp.nice = t[level][1]; lp.max_lazy = t[level][2]; lp.lazy_parse = t[level][3]; lp.use_h3 = t[level][4]; lp.use_h4 = t[level][5];
+    return lp;
 }
 
 int ensure_scratch(gzb_ctx* ctx, uint32_t nchunks, uint32_t chunk)
@@ -162,8 +179,20 @@ int gzb_create(int device, gzb_ctx** out)
     if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return GZB_E_NO_DEVICE; }
     if (prop.major < 10) { delete ctx; return GZB_E_NO_DEVICE; }     // sm_100a code only
     ctx->n_sm = prop.multiProcessorCount;
-    const char* bc = getenv("GZB_BATCH_CHUNKS");
-    if (bc && atoi(bc) > 0) ctx->batch_chunks = (uint32_t)atoi(bc);
+    auto env_int = [](const char* name, long long lo, long long hi, long long dflt) -> long long {
+        const char* e = getenv(name);
+        if (!e || !*e) return dflt;
+        const long long v = atoll(e);
+        return v < lo || v > hi ? dflt : v;                                  // out of range: ignored
+    };
+    ctx->batch_chunks = (uint32_t)env_int("GZB_BATCH_CHUNKS", 1, 1 << 20, 4096);
+    ctx->tune.pw = (int)env_int("GZB_PW", 8, 16, 0); if (ctx->tune.pw != 8 && ctx->tune.pw != 16) ctx->tune.pw = 0;
+    ctx->tune.help = (int)env_int("GZB_HELP", 0, 3, -1);
+    ctx->tune.rolemap = (int)env_int("GZB_ROLEMAP", 0, 2, -1);
+    ctx->tune.max_run = (int)env_int("GZB_MAX_RUN", 1, 64, 32);
+    ctx->tune.force_run = (int)env_int("GZB_FORCE_RUN", 1, 4096, 0);
+    ctx->tune.host_batch = (uint64_t)env_int("GZB_HOST_BATCH_MB", 1, 1 << 16, 512) << 20;
+    ctx->tune.host_edge = (uint64_t)env_int("GZB_HOST_EDGE_MB", 0, 1 << 16, 64) << 20;
     uint32_t tab[CRC_TAB_WORDS];
     build_crc_tables(tab);
     memcpy(ctx->h_x2n, tab + 1024, sizeof(ctx->h_x2n));
@@ -192,7 +221,8 @@ void gzb_destroy(gzb_ctx* ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->scr.tokens); cudaFree(ctx->scr.blocks); cudaFree(ctx->scr.chunks);
-    cudaFree(ctx->d_tab); cudaFree(ctx->d_cursor); cudaFree(ctx->d_work);
+    cudaFree(ctx->d_tab); cudaFree(ctx->d_cursor); cudaFree(ctx->d_work); cudaFree(ctx->d_crc_recs);
+    if (ctx->h_crc_recs) cudaFreeHost(ctx->h_crc_recs);
     if (ctx->s_in) cudaStreamSynchronize(ctx->s_in);
     if (ctx->s_out) cudaStreamSynchronize(ctx->s_out);
     for (int i = 0; i < 2; i++) {
@@ -234,11 +264,12 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     const uint64_t nchunks64 = (n + chunk - 1) / chunk;
     const uint32_t bpc = (chunk + BLOCK_SPAN - 1) / BLOCK_SPAN;
     LevelParams lp = level_params(level);
-    lp.parse_warps = getenv("GZB_PW") ? atoi(getenv("GZB_PW")) : (level <= 2 ? 16 : 8);
-    lp.flow = getenv("GZB_FLOW") ? atoi(getenv("GZB_FLOW")) : (level >= 7 ? 2 : level >= 5 ? 1 : 0);
-    lp.spin_ns = getenv("GZB_SPIN") ? atoi(getenv("GZB_SPIN")) : 100;
-    // warp roles: measured on B200 (tools/variant_sweep.py, profiles/r01f_variant_sweep.txt)
-    lz77_role_map(lp, getenv("GZB_ROLEMAP") ? atoi(getenv("GZB_ROLEMAP")) : (lp.flow && lp.parse_warps == 8 ? 11 : 0));
+    // scheduling by level, measured on B200 (tools/variant_sweep.py, profiles/)
+    lp.parse_warps = ctx->tune.pw ? ctx->tune.pw : (level <= 2 ? 16 : 8);
+    const int help = ctx->tune.help >= 0 ? ctx->tune.help : (level >= 7 ? 3 : 0);
+    lp.help_ins = help & 1; lp.help_parse = (help >> 1) & 1;
+    lp.max_run = ctx->tune.max_run; lp.force_run = ctx->tune.force_run;
+    lz77_role_map(lp, ctx->tune.rolemap >= 0 ? ctx->tune.rolemap : 2);
     ctx->n_sub_timed = 0;
 
     CU(ctx, cudaMemsetAsync(ctx->d_cursor, 0, sizeof(Cursor), st));
@@ -286,8 +317,10 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
         if (timed) { CU(ctx, cudaEventRecord(ev[4], st)); }
         launch_pack(d_in + off, chunk, ctx->scr.tokens, ctx->scr.blocks, ctx->scr.chunks, nch, bpc, d_out, st);
         if (timed) { CU(ctx, cudaEventRecord(ev[5], st)); ctx->n_sub_timed = (int)sb + 1; }
-        if ((flags & GZB_F_VERIFY) && sb == 0 && getenv("GZB_DEBUG_CORRUPT_AT"))      // fault injection for the tests of k_verify
-            CU(ctx, cudaMemsetAsync(d_out + strtoull(getenv("GZB_DEBUG_CORRUPT_AT"), nullptr, 10), 0xA5, 1, st));
+#ifdef GZB_TESTING
+        if ((flags & GZB_F_VERIFY) && sb == 0 && ctx->test_corrupt_at >= 0 && (uint64_t)ctx->test_corrupt_at < gzb_bound(n, flags))
+            CU(ctx, cudaMemsetAsync(d_out + ctx->test_corrupt_at, 0xA5, 1, st));
+#endif
         if (flags & GZB_F_VERIFY)
             launch_verify(d_in + off, chunk, dict, h, ctx->scr.chunks, nch, d_out, fin, c0, ctx->d_cursor, st);
     }
@@ -315,21 +348,20 @@ void cursor_to_result(const Cursor& c, gzb_result* r)
 
 extern "C" {
 
-int gzb_deflate_device_async(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
-                             uint8_t* d_out, uint64_t out_cap, void* stream)
+// the two halves of a device call; ctx->mu is held by the caller
+static int submit_locked(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
+                         uint8_t* d_out, uint64_t out_cap, void* stream)
 {
-    if (!ctx) return GZB_E_ARG;
-    std::lock_guard<std::mutex> g(ctx->mu);
+    // one call in flight per context: its cursor, work counters and scratch are shared
+    if (ctx->pending) return fail(ctx, GZB_E_ARG, "a call is already pending on this context: gzb_deflate_wait() first");
     cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
     int rc = enqueue_deflate(ctx, level, flags, d_in, n, halo, d_out, out_cap, st);
     if (rc == GZB_OK) { ctx->pending = true; ctx->pending_n = n; ctx->pending_stream = st; }
+    else if (ctx->stream) { cudaStreamSynchronize(st); (void)cudaGetLastError(); }     // nothing of a failed submit stays in flight
     return rc;
 }
-
-int gzb_deflate_wait(gzb_ctx* ctx, gzb_result* result)
+static int wait_locked(gzb_ctx* ctx, gzb_result* result)
 {
-    if (!ctx) return GZB_E_ARG;
-    std::lock_guard<std::mutex> g(ctx->mu);
     if (!ctx->pending) return fail(ctx, GZB_E_ARG, "nothing pending");
     ctx->pending = false;
     CU(ctx, cudaSetDevice(ctx->device));
@@ -343,13 +375,35 @@ int gzb_deflate_wait(gzb_ctx* ctx, gzb_result* result)
     return ctx->h_cursor->status;
 }
 
+int gzb_deflate_device_async(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
+                             uint8_t* d_out, uint64_t out_cap, void* stream)
+{
+    if (!ctx) return GZB_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    return submit_locked(ctx, level, flags, d_in, n, halo, d_out, out_cap, stream);
+}
+
+int gzb_deflate_wait(gzb_ctx* ctx, gzb_result* result)
+{
+    if (!ctx) return GZB_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    return wait_locked(ctx, result);
+}
+
 int gzb_deflate_device(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in, uint64_t n, uint32_t halo,
                        uint8_t* d_out, uint64_t out_cap, gzb_result* result, void* stream)
 {
-    int rc = gzb_deflate_device_async(ctx, level, flags, d_in, n, halo, d_out, out_cap, stream);
+    if (!ctx) return GZB_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->mu);                                  // one critical section: nobody slips in between
+    int rc = submit_locked(ctx, level, flags, d_in, n, halo, d_out, out_cap, stream);
     if (rc != GZB_OK) return rc;
-    return gzb_deflate_wait(ctx, result);
+    return wait_locked(ctx, result);
 }
+
+#ifdef GZB_TESTING
+// test build only (csrc/build/libgzb200_testing.so): the next GZB_F_VERIFY calls overwrite one output byte before k_verify runs
+int gzb_test_corrupt_at(gzb_ctx* ctx, long long offset) { if (!ctx) return GZB_E_ARG; ctx->test_corrupt_at = offset; return GZB_OK; }
+#endif
 
 // debugging aid (not in gzb200.h): cycle counters of k_lz77's pipeline phases, see k_lz77.cu
 int gzb_debug_lzprof(gzb_ctx* ctx, unsigned long long* out16, int reset)
@@ -434,14 +488,13 @@ bool is_pinned(const void* p)
 // Batch boundaries of the host path.  The H2D copy of the first batch and the D2H copy of the last one have nothing to
 // hide behind, so a large input starts with growing batches, ends with a small one (EDGE) and runs in HOST_BATCH pieces in
 // between.
-static std::vector<uint64_t> host_batch_plan(uint64_t n, uint64_t HOST_BATCH)
+static std::vector<uint64_t> host_batch_plan(uint64_t n, uint64_t HOST_BATCH, uint64_t EDGE)
 {
-    const uint64_t EDGE = (getenv("GZB_HOST_EDGE_MB") ? (uint64_t)atoi(getenv("GZB_HOST_EDGE_MB")) : 64ull) << 20;   // multiple of both chunk sizes
     std::vector<uint64_t> boff;
     boff.push_back(0);
     if (EDGE && EDGE < HOST_BATCH && n > 4 * EDGE) {
         // sizes EDGE, 3 EDGE, 9 EDGE ... up to HOST_BATCH (a batch's H2D copy hides behind the kernels of the one before
-        // it as long as it is at most ~3 times as large: PCIe moves ~55 GB/s, the kernels take ~18 GB/s at -6), the
+        // it as long as it is at most ~3 times as large: PCIe moves ~55 GB/s, the kernels take ~20 GB/s at -6), the
         // last batch <= EDGE
         const uint64_t rem = n - EDGE, tail = rem % EDGE ? rem % EDGE : EDGE, end_main = n - tail;
         uint64_t pos = 0, sz = EDGE;
@@ -451,16 +504,14 @@ static std::vector<uint64_t> host_batch_plan(uint64_t n, uint64_t HOST_BATCH)
     boff.push_back(n);
     return boff;
 }
-static uint64_t host_batch_bytes()
-{
-    const uint64_t mb = getenv("GZB_HOST_BATCH_MB") ? (uint64_t)atoi(getenv("GZB_HOST_BATCH_MB")) : 512ull;
-    return (mb ? mb : 1ull) << 20;                                          // multiple of both chunk sizes
-}
 
+// host arithmetic only (no context): the sizes come from the same environment variables gzb_create reads
 extern "C" int gzb_host_batch_plan(uint64_t n, uint64_t* off, int cap)
 {
     if (!off) return GZB_E_ARG;
-    const std::vector<uint64_t> b = host_batch_plan(n, host_batch_bytes());
+    const char* eb = getenv("GZB_HOST_BATCH_MB"); const char* ee = getenv("GZB_HOST_EDGE_MB");
+    const uint64_t mb = eb && atoll(eb) > 0 ? (uint64_t)atoll(eb) : 512ull, edge = ee && atoll(ee) >= 0 ? (uint64_t)atoll(ee) : 64ull;
+    const std::vector<uint64_t> b = host_batch_plan(n, mb << 20, edge << 20);
     if ((size_t)cap < b.size()) return GZB_E_ARG;
     for (size_t i = 0; i < b.size(); i++) off[i] = b[i];
     return (int)b.size() - 1;
@@ -480,10 +531,11 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
     const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
     const uint32_t dsz = rs ? 0u : GZB_DICT;
-    const uint64_t HOST_BATCH = host_batch_bytes();
     std::lock_guard<std::mutex> g(ctx->mu);
+    if (ctx->pending) return fail(ctx, GZB_E_ARG, "a device call is pending on this context: gzb_deflate_wait() first");
     CU(ctx, cudaSetDevice(ctx->device));
-    const std::vector<uint64_t> boff = host_batch_plan(n, HOST_BATCH);     // batch i = [boff[i], boff[i + 1])
+    const uint64_t HOST_BATCH = ctx->tune.host_batch;
+    const std::vector<uint64_t> boff = host_batch_plan(n, HOST_BATCH, ctx->tune.host_edge);   // batch i = [boff[i], boff[i + 1])
     const uint64_t nbatch = boff.size() - 1;
     const uint64_t bmax = n < HOST_BATCH ? n : HOST_BATCH;
     const bool pin_in = n && is_pinned(in) && (!dict || is_pinned(dict)), pin_out = is_pinned(out);
@@ -525,35 +577,78 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
         pend[sl].live = false;
         return GZB_OK;
     };
-
-    if ((rc = issue_h2d(0)) != GZB_OK) return rc;
-    for (uint64_t i = 0; i < nbatch; i++) {
-        const int sl = (int)(i & 1);
-        const uint64_t off = boff[i], nb = batch_len(i);
-        const uint32_t halo = ((off == 0 ? dict != nullptr : true) && dsz) ? dsz : 0u;
-        const uint32_t f = (flags & ~GZB_F_FINAL) | ((i + 1 == nbatch && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
-        if ((rc = drain(sl)) != GZB_OK) return rc;                          // d_out[sl] / h_out[sl] are free again
-        CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->e_in[sl], 0));
-        rc = enqueue_deflate(ctx, level, f, ctx->d_in[sl] + dsz, nb, halo, ctx->d_out[sl], ctx->dev_out_cap, ctx->stream);
-        if (rc != GZB_OK) return rc;
-        CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
-        if (i + 1 < nbatch && (rc = issue_h2d(i + 1)) != GZB_OK) return rc; // overlaps the kernels of batch i
-        CU(ctx, cudaStreamSynchronize(ctx->stream));                        // out_bytes of batch i is known now
-        const Cursor c = *ctx->h_cursor;
-        if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
-        if (c.verify_bad) return verify_status(ctx, c);
-        if (c.in_bytes != nb) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
-        if (opos + c.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
-        if (c.out_bytes) CU(ctx, cudaMemcpyAsync(pin_out ? out + opos : ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));
-        CU(ctx, cudaEventRecord(ctx->e_out[sl], ctx->s_out));
-        pend[sl].bytes = c.out_bytes; pend[sl].opos = opos; pend[sl].live = true;
-        opos += c.out_bytes;
-        total.crc32 = gzb_crc32_combine(total.crc32, c.crc, nb);
-        total.in_bytes += nb; total.n_chunks += c.n_chunks; total.n_blocks += c.n_blocks;
+    auto pipeline = [&]() -> int {
+        int r;
+        if ((r = issue_h2d(0)) != GZB_OK) return r;
+        for (uint64_t i = 0; i < nbatch; i++) {
+            const int sl = (int)(i & 1);
+            const uint64_t off = boff[i], nb = batch_len(i);
+            const uint32_t halo = ((off == 0 ? dict != nullptr : true) && dsz) ? dsz : 0u;
+            const uint32_t f = (flags & ~GZB_F_FINAL) | ((i + 1 == nbatch && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
+            if ((r = drain(sl)) != GZB_OK) return r;                        // d_out[sl] / h_out[sl] are free again
+            CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->e_in[sl], 0));
+            r = enqueue_deflate(ctx, level, f, ctx->d_in[sl] + dsz, nb, halo, ctx->d_out[sl], ctx->dev_out_cap, ctx->stream);
+            if (r != GZB_OK) return r;
+            CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
+            if (i + 1 < nbatch && (r = issue_h2d(i + 1)) != GZB_OK) return r; // overlaps the kernels of batch i
+            CU(ctx, cudaStreamSynchronize(ctx->stream));                    // out_bytes of batch i is known now
+            const Cursor c = *ctx->h_cursor;
+            if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
+            if (c.verify_bad) return verify_status(ctx, c);
+            if (c.in_bytes != nb) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
+            if (opos + c.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
+            if (c.out_bytes) CU(ctx, cudaMemcpyAsync(pin_out ? out + opos : ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));
+            CU(ctx, cudaEventRecord(ctx->e_out[sl], ctx->s_out));
+            pend[sl].bytes = c.out_bytes; pend[sl].opos = opos; pend[sl].live = true;
+            opos += c.out_bytes;
+            total.crc32 = gzb_crc32_combine(total.crc32, c.crc, nb);
+            total.in_bytes += nb; total.n_chunks += c.n_chunks; total.n_blocks += c.n_blocks;
+        }
+        for (int sl = 0; sl < 2; sl++) if ((r = drain(sl)) != GZB_OK) return r;
+        return GZB_OK;
+    };
+    rc = pipeline();
+    if (rc != GZB_OK) {
+        // One exit for every failure: nothing stays in flight.  The H2D copy of the next batch and the D2H copies of the
+        // earlier ones may still be running -- into the caller's own buffers when those are pinned -- so all three streams
+        // are drained before the caller gets its memory back; the detail text of the first failure is kept.
+        char keep[sizeof(ctx->err)]; memcpy(keep, ctx->err, sizeof(keep));
+        cudaStreamSynchronize(ctx->s_in); cudaStreamSynchronize(ctx->stream); cudaStreamSynchronize(ctx->s_out);
+        (void)cudaGetLastError();
+        memcpy(ctx->err, keep, sizeof(keep));
+        return rc;
     }
-    for (int sl = 0; sl < 2; sl++) if ((rc = drain(sl)) != GZB_OK) return rc;
     total.out_bytes = opos; total.status = GZB_OK;
     if (result) *result = total;
+    return GZB_OK;
+}
+
+// ctx->mu is held by the caller
+static int crc32_device_locked(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, uint64_t n, uint32_t* crc_out, cudaStream_t st)
+{
+    constexpr uint64_t SUB = 65536;                                         // chunks per launch
+    const uint32_t chunk = GZB_CHUNK;
+    if (n && !ctx->d_crc_recs) {                                            // scratch of the context, allocated on first use
+        if (cudaMalloc(&ctx->d_crc_recs, sizeof(ChunkRec) * SUB) != cudaSuccess ||
+            cudaMallocHost(&ctx->h_crc_recs, sizeof(ChunkRec) * SUB) != cudaSuccess) {
+            cudaFree(ctx->d_crc_recs); ctx->d_crc_recs = nullptr; (void)cudaGetLastError();
+            return fail(ctx, GZB_E_NOMEM, "crc32 scratch");
+        }
+    }
+    uint32_t acc = crc;
+    const uint64_t nchunks64 = (n + chunk - 1) / chunk;
+    for (uint64_t c0 = 0; c0 < nchunks64; c0 += SUB) {
+        const uint32_t nch = (uint32_t)((nchunks64 - c0) < SUB ? (nchunks64 - c0) : SUB);
+        const uint64_t off = c0 * chunk, nb = (n - off) < (uint64_t)nch * chunk ? (n - off) : (uint64_t)nch * chunk;
+        launch_crc32(d_in + off, nb, chunk, nch, ctx->d_crc_recs, ctx->d_tab, st);
+        CU(ctx, cudaMemcpyAsync(ctx->h_crc_recs, ctx->d_crc_recs, sizeof(ChunkRec) * nch, cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaStreamSynchronize(st));
+        for (uint32_t i = 0; i < nch; i++) {
+            uint64_t len = (uint64_t)(i + 1) * chunk <= nb ? chunk : nb - (uint64_t)i * chunk;
+            acc = crc_shift(ctx->h_x2n, acc, len) ^ ctx->h_crc_recs[i].crc;
+        }
+    }
+    *crc_out = acc;
     return GZB_OK;
 }
 
@@ -563,52 +658,26 @@ int gzb_crc32_device(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, uint64_t n
     if ((uintptr_t)d_in & 15u) return fail(ctx, GZB_E_ARG, "d_in must be 16-byte aligned");
     std::lock_guard<std::mutex> g(ctx->mu);
     CU(ctx, cudaSetDevice(ctx->device));
-    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
-    const uint32_t chunk = GZB_CHUNK;
-    uint32_t acc = crc;
-    const uint64_t nchunks64 = (n + chunk - 1) / chunk;
-    const uint64_t sub = nchunks64 < 65536 ? nchunks64 : 65536;
-    ChunkRec* d_recs = nullptr; ChunkRec* h_recs = nullptr;
-    if (n) {
-        CU(ctx, cudaMalloc(&d_recs, sizeof(ChunkRec) * sub));
-        h_recs = (ChunkRec*)malloc(sizeof(ChunkRec) * sub);
-        if (!h_recs) { cudaFree(d_recs); return fail(ctx, GZB_E_NOMEM, "malloc"); }
-    }
-    for (uint64_t c0 = 0; c0 < nchunks64; c0 += sub) {
-        const uint32_t nch = (uint32_t)((nchunks64 - c0) < sub ? (nchunks64 - c0) : sub);
-        const uint64_t off = c0 * chunk, nb = (n - off) < (uint64_t)nch * chunk ? (n - off) : (uint64_t)nch * chunk;
-        launch_crc32(d_in + off, nb, chunk, nch, d_recs, ctx->d_tab, st);
-        cudaError_t e = cudaMemcpyAsync(h_recs, d_recs, sizeof(ChunkRec) * nch, cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        if (e != cudaSuccess) { cudaFree(d_recs); free(h_recs); return fail(ctx, GZB_E_CUDA, "crc32", e); }
-        for (uint32_t i = 0; i < nch; i++) {
-            uint64_t len = (uint64_t)(i + 1) * chunk <= nb ? chunk : nb - (uint64_t)i * chunk;
-            acc = crc_shift(ctx->h_x2n, acc, len) ^ h_recs[i].crc;
-        }
-    }
-    cudaFree(d_recs); free(h_recs);
-    *crc_out = acc;
-    return GZB_OK;
+    return crc32_device_locked(ctx, crc, d_in, n, crc_out, stream ? (cudaStream_t)stream : ctx->stream);
 }
 
 int gzb_crc32_host(gzb_ctx* ctx, uint32_t crc, const uint8_t* in, uint64_t n, uint32_t* crc_out)
 {
     if (!ctx || !crc_out || (n && !in)) return GZB_E_ARG;
     const uint64_t B = 128ull << 20;
+    std::lock_guard<std::mutex> g(ctx->mu);                                 // held across staging, copy and kernel of every batch
+    if (ctx->pending) return fail(ctx, GZB_E_ARG, "a device call is pending on this context: gzb_deflate_wait() first");
+    CU(ctx, cudaSetDevice(ctx->device));
     uint32_t acc = crc;
     for (uint64_t off = 0; off < n; off += B) {
         const uint64_t nb = (n - off) < B ? (n - off) : B;
-        {
-            std::lock_guard<std::mutex> g(ctx->mu);
-            CU(ctx, cudaSetDevice(ctx->device));
-            int rc = ensure_dev(ctx, GZB_DICT + nb + 16, 0);
-            if (rc == GZB_OK) rc = ensure_pinned(ctx, GZB_DICT + nb + 16, 0);
-            if (rc != GZB_OK) return rc;
-            memcpy(ctx->h_in[0], in + off, nb);
-            CU(ctx, cudaMemcpyAsync(ctx->d_in[0], ctx->h_in[0], nb, cudaMemcpyHostToDevice, ctx->stream));
-        }
-        int rc = gzb_crc32_device(ctx, acc, ctx->d_in[0], nb, &acc, ctx->stream);
+        int rc = ensure_dev(ctx, GZB_DICT + nb + 16, 0);
+        if (rc == GZB_OK) rc = ensure_pinned(ctx, GZB_DICT + nb + 16, 0);
         if (rc != GZB_OK) return rc;
+        memcpy(ctx->h_in[0], in + off, nb);
+        CU(ctx, cudaMemcpyAsync(ctx->d_in[0], ctx->h_in[0], nb, cudaMemcpyHostToDevice, ctx->stream));
+        rc = crc32_device_locked(ctx, acc, ctx->d_in[0], nb, &acc, ctx->stream);
+        if (rc != GZB_OK) { cudaStreamSynchronize(ctx->stream); (void)cudaGetLastError(); return rc; }
     }
     *crc_out = acc;
     return GZB_OK;

@@ -35,16 +35,16 @@ constexpr int      HDR_BYTES   = 608;             // worst case 14 + 57 + 316*14
 // (lib/zlib/deflate.c:134-146); depth replaces max_chain (DESIGN.md "Level semantics").
 struct LevelParams {
     int depth, nice, max_lazy, lazy_parse, use_h3, use_h4;
-    int parse_warps;                         // 8 or 16: size of k_lz77's parser group (no effect on the result)
-    int spin_ns;                             // k_lz77 (flow): sleep between two polls of a pipeline counter
-    int flow;                                // k_lz77: search warps flow from tile to tile (no effect on the result)
-    // k_lz77: what each of the 32 warps of a CTA does (no effect on the result; lz77_role_map).  role_b0..3: one byte per
-    // warp (warps 0-7, 8-15, ...): 0-2 inserter of the 6-byte / 3-byte / 4-byte table, 3 loader, 4 search, 8 + i parser i;
-    // role_mask: bit w set = warp w is not a search warp; ins0_loads: no loader warp, the 6-byte inserter loads the tiles.
-    // (Scalars, not arrays: an array indexed by the warp number would move the whole struct to local memory.)
+    // ---- scheduling of k_lz77: none of these changes a byte of output (tests/ force each of them) ----
+    int parse_warps;                         // 8 or 16: size of the parser group
+    int help_ins, help_parse;                // the inserter / parser warps take search groups when their own tile is done
+    int max_run, force_run;                  // longest run of chained chunks a launch may pick; > 0: run length forced (tests)
+    // what each of the 32 warps of a CTA does (lz77_role_map).  role_b0..3: one byte per warp (warps 0-7, 8-15, ...):
+    // 0-2 inserter of the 6-byte / 3-byte / 4-byte table, 4 search, 8 + i parser i; role_mask: bit w set = warp w is
+    // not a pure search warp.  (Scalars, not arrays: an array indexed by the warp number would move the whole struct to
+    // local memory.)
     unsigned long long role_b0, role_b1, role_b2, role_b3;
     uint32_t role_mask;
-    int ins0_loads;
 };
 
 // One deflate block.  Written by k_lz77 (histograms, token range, input range),
@@ -177,7 +177,7 @@ void launch_verify(const uint8_t* in, uint32_t chunk, uint32_t dict, uint32_t ha
 void launch_pack(const uint8_t* in, uint32_t chunk, const uint32_t* tokens, const BlockRec* blocks, const ChunkRec* chunks,
                  uint32_t nchunks, uint32_t bpc, uint8_t* out, cudaStream_t st);
 cudaError_t lz77_configure();
-void lz77_role_map(LevelParams& lp, int preset);   // fills lp.role / ridx / n_role / ins0_loads from lp.parse_warps
+void lz77_role_map(LevelParams& lp, int layout);   // fills lp.role_b0..3 / role_mask from lp.parse_warps
 cudaError_t lz77_read_prof(unsigned long long* out16, int reset);
 
 }  // namespace gzb

@@ -65,6 +65,7 @@ void gzm_level_params(int level, gzm_params *p)
     p->lazy_parse = level >= 4;
     p->maxd = GZM_MAXD; p->hbits = GZM_HBITS; p->block_span = GZM_BLOCK_SPAN;
     p->chunk = 131072; p->dict = 32768; p->use_h3 = 1; p->use_h4 = 1;
+    p->good_cut = 0;    /* measured and left off: +0.3..1.1 % bytes for -9 % compare trips per 32-position group */
 }
 
 /* ---------------- match finder ---------------- */
@@ -74,6 +75,21 @@ uint32_t gzm_hash4(uint32_t v) { return (v * 0x9E3779B1u) >> (32 - GZM_H4BITS); 
 uint32_t gzm_hash3(uint32_t v) { return ((v << 8) * 0x9E3779B1u) >> (32 - GZM_H3BITS); }
 
 static int common_len(const uint8_t *a, const uint8_t *b, int maxlen) { int l = 0; while (l < maxlen && a[l] == b[l]) l++; return l; }
+#ifdef GZM_STATS
+/* cost proxies for the lockstep search of k_lz77 (tools/ experiments only): per 32-position group, rounds = max over its
+ * positions, compare trips per round = max over its positions.  [0] positions [1] chain steps [2] measured candidates
+ * [3] trips (per position) [4] groups [5] lockstep rounds [6] lockstep trips */
+unsigned long long gzm_stats[8];
+static int g_rounds[32], g_trips[32][20];
+static void stats_group_flush(void)
+{
+    int mr = 0;
+    for (int i = 0; i < 32; i++) if (g_rounds[i] > mr) mr = g_rounds[i];
+    gzm_stats[4]++; gzm_stats[5] += (unsigned)mr;
+    for (int r = 0; r < mr && r < 20; r++) { int mt = 0; for (int i = 0; i < 32; i++) if (g_trips[i][r] > mt) mt = g_trips[i][r]; gzm_stats[6] += (unsigned)mt; }
+    memset(g_rounds, 0, sizeof(g_rounds)); memset(g_trips, 0, sizeof(g_trips));
+}
+#endif
 
 /* stream = dict||chunk, D = dict length, n = total stream length.  Positions < D are inserted only.
  * bytes beyond the stream end read as zero for hashing (positions n-5..n-1). */
@@ -103,13 +119,39 @@ void gzm_find_matches(const gzm_params *P, const uint8_t *s, int D, int n, uint1
         int nice = P->nice < maxlen ? P->nice : maxlen;
         /* the last five positions of a chunk, whose six hashed bytes would run past its end, do not walk a chain
          * (what follows the chunk is the next chunk's business: the engine may or may not have it at hand) */
-        int c = maxlen >= 6 ? link[p] : -1, depth = P->depth;
-        while (c >= 0 && p - c <= limit && depth-- > 0) {
-            if (maxlen > best && s[c + best] == s[p + best]) {
-                int l = common_len(s + c, s + p, maxlen);
-                if (l > best) { best = l; bdist = p - c; if (l >= nice) break; }
+        int c = maxlen >= 6 ? link[p] : -1, depth = P->depth, cut = 0;
+        /* The walk goes in ROUNDS, as the kernel's lanes do: up to GZM_WALK_STEPS chain steps in which a candidate that
+         * passes the one-byte filter (against the best length at the start of the round) is only noted -- a second noted
+         * candidate ends the round early --, then the noted ones are measured in chain order, strictly longer wins.
+         * Without the good_length rule this equals the one-candidate-at-a-time walk.  With it (levels 4-9, cf.
+         * `if (s->prev_length >= s->good_match) chain_length >>= 2`, lib/zlib/deflate.c:1254-1257): once the best match
+         * has reached good_length at the end of a round, the remaining candidate budget is quartered, once. */
+        while (c >= 0 && p - c <= limit && depth > 0) {
+            int pend[2], npend = 0;
+            const int fbest = best;
+#ifdef GZM_STATS
+            const int lane_ = (p - D) & 31, r_ = g_rounds[lane_] < 19 ? g_rounds[lane_] : 19; g_rounds[lane_]++;
+#endif
+            for (int st = 0; st < GZM_WALK_STEPS && npend < 2; st++) {
+                if (!(c >= 0 && p - c <= limit && depth > 0)) break;
+                if (s[c + fbest] == s[p + fbest]) pend[npend++] = c;
+                c = link[c]; depth--;
+#ifdef GZM_STATS
+                gzm_stats[1]++;
+#endif
             }
-            c = link[c];
+            int stop = 0;
+            for (int i = 0; i < npend && !stop; i++) {
+                const int cand = pend[i];
+                if (i == 1 && s[cand + best] != s[p + best]) continue;
+                int l = common_len(s + cand, s + p, maxlen);
+#ifdef GZM_STATS
+                gzm_stats[2]++; gzm_stats[3] += (unsigned)(l / 16 + 1); g_trips[lane_][r_] += l / 16 + 1;
+#endif
+                if (l > best) { best = l; bdist = p - cand; if (l >= nice || l >= maxlen) stop = 1; }
+            }
+            if (stop) break;
+            if (P->good_cut && !cut && best >= P->good) { cut = 1; depth >>= 2; }
         }
         /* nothing of 6+ on the chain: try the most recent 4-byte twin (single-entry table) */
         if (best < 6 && P->use_h4 && prev4 >= 0 && p - prev4 <= (limit < 32767 ? limit : 32767) && maxlen >= 4) {
@@ -124,6 +166,10 @@ void gzm_find_matches(const gzm_params *P, const uint8_t *s, int D, int n, uint1
         if (best == 3 && bdist > GZM_TOO_FAR) best = 2;       /* TOO_FAR, deflate.c:110-112,1972-1981 */
         if (best < 3) { mlen[p - D] = 0; mdist[p - D] = 0; }
         else { mlen[p - D] = (uint16_t)best; mdist[p - D] = (uint16_t)bdist; }
+#ifdef GZM_STATS
+        gzm_stats[0]++;
+        if (((p - D) & 31) == 31 || p == n - 1) stats_group_flush();
+#endif
     }
     free(head); free(head3); free(head4); free(link);
 }

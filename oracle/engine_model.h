@@ -10,6 +10,7 @@ extern "C" {
 #define GZM_HBITS       14
 #define GZM_H3BITS      12                        /* single-entry table of most recent 3-byte twins */
 #define GZM_H4BITS      12                        /* single-entry table of most recent 4-byte twins */
+#define GZM_WALK_STEPS  4                         /* chain steps per round of the walk (k_lz77 search_group)  */
 #define GZM_TILE        2048                      /* positions per pipeline step of the LZ77 kernel */
 #define GZM_MAXD        32768                     /* farthest match (the link ring is 32768+2*TILE) */
 #define GZM_TOO_FAR     4096                      /* lib/zlib/deflate.c:110-112                      */
@@ -22,6 +23,7 @@ typedef struct gzm_params {
     int maxd, hbits, block_span, chunk, dict;
     int use_h3;                                   /* fall back to the most recent 3-byte twin when nothing longer exists */
     int use_h4;                                   /* ... and to the most recent 4-byte twin when the chain gives < 6  */
+    int good_cut;                                 /* quarter the remaining candidate budget once the best match reaches `good` */
 } gzm_params;
 
 typedef struct gzm_block_plan {
