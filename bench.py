@@ -1,19 +1,34 @@
 #!/usr/bin/env python
-"""bench.py -- BASELINE.json's metric on BASELINE.json's config.
+"""bench.py -- BASELINE.json's metric on BASELINE.json's configs.
 
-  metric   compress INPUT GB/s (1e9 B/s) at level -6, whole job over N GPUs
-  workload configs[1]: parallel mode -6, 128 KiB chunks, 32 KiB dictionary priming, 4 GiB synthetic text per GPU
+  metric   compress INPUT GB/s (1e9 B/s), whole job over N GPUs
   step     one pass of the hot path (CRC-32, LZ77, Huffman, layout, pack) over the whole workload
   value    device-resident: input already in HBM, output left in HBM, CUDA events on the launching stream
   e2e      the same through the host-buffer C-ABI call (gzb_deflate_host) on pinned host buffers: H2D + kernels + D2H inside
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--mib M] [--level L] [--corpus KIND]
-Under torchrun (N > 1) every rank compresses its own contiguous shard (weak scaling, no data-path collective).
+  configs (BASELINE.json `configs`), --config K:
+    0  CPU anchor: reference `gzip -6` single stream on 256 MiB text (+ the engine on the same bytes)
+    1  parallel mode -6, 128 KiB chunks + 32 KiB dictionary, 4 GiB synthetic text on 1 GPU          [default at N = 1]
+    2  -9 on 4 GiB mixed text/binary/random
+    3  -1 on 4 GiB incompressible random data (stored blocks: the CRC / packing-bound path)
+    4  64 GiB text sharded by chunk over the N GPUs, bodies concatenated into ONE member, CRCs folded with crc32_combine
+                                                                                                 [default at N > 1]
+  Every line carries the parity gates of its config: round trip, CRC-32 vs zlib, size_vs_ref = engine bytes / reference
+  bytes on the SAME input at the same level (asserted <= 1.03 before a number is printed).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config K] [--mib M] [--level L] [--corpus KIND]
+Under torchrun (N > 1) every rank compresses its own contiguous shard (no data-path collective: NCCL carries the timing
+scalar and barriers only); rank 0 then assembles and checks the single member outside the timed region.
 """
-import argparse, json, os, subprocess, sys, threading, time
+import argparse, ctypes, json, os, shutil, subprocess, sys, tempfile, threading, time, zlib
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+REFGZIP = os.path.join(ROOT, "oracle", "_ref", "refgzip")
+REFZ = os.path.join(ROOT, "oracle", "_ref", "librefz.so")
+RATIO_TOL = 1.03
+CONFIGS = {0: dict(level=6, corpus="text", mib=256), 1: dict(level=6, corpus="text", mib=4096), 2: dict(level=9, corpus="mixed", mib=4096),
+           3: dict(level=1, corpus="random", mib=4096), 4: dict(level=6, corpus="text", mib=65536)}
 
 
 def parse():
@@ -22,11 +37,23 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gzb200", choices=["gzb200", "reference"])
-    ap.add_argument("--mib", type=int, default=4096, help="MiB of input per GPU (BASELINE configs[1]: 4096)")
-    ap.add_argument("--level", type=int, default=6)
-    ap.add_argument("--corpus", default="text")
+    ap.add_argument("--config", type=int, default=None, choices=sorted(CONFIGS), help="BASELINE.json configs[K] (default: 1 at N = 1, 4 at N > 1)")
+    ap.add_argument("--mib", type=int, default=None, help="override: MiB of input (per GPU; for config 4: in total)")
+    ap.add_argument("--level", type=int, default=None)
+    ap.add_argument("--corpus", default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-configs", action="store_true", help="N = 1 default run: skip the short configs[0], [2], [3] lines")
+    ap.add_argument("--member-check", default="auto", choices=["auto", "full", "seams", "off"],
+                    help="config 4: decode the whole concatenated member with refgzip -d (full: minutes for 64 GiB), or only every shard seam")
     return ap.parse_args()
+
+
+def workload_name(cfg, level, corpus, mib, world):
+    if cfg == 4:
+        return f"configs[4]: {mib} MiB synthetic {corpus} sharded by chunk over {world} GPU(s), -{level}, bodies concatenated into one member + crc32_combine"
+    if cfg == 0:
+        return f"configs[0]: -{level} on {mib} MiB synthetic {corpus} (the reference's single-stream CPU anchor; engine: one member on the chunk grid)"
+    return f"configs[{cfg}]: parallel mode -{level}, 128 KiB chunks + 32 KiB dictionary, {mib} MiB synthetic {corpus} per GPU"
 
 
 class ClockSampler(threading.Thread):
@@ -62,57 +89,304 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_reference(level, corpus, sample_mib, threads):
-    """The reference's own CPU path (oracle/_ref/refgzip = src/zip.c + src/parallel.c + zlib 1.2.11) on host cores."""
-    import gzippier_b200 as gz
-    exe = os.path.join(ROOT, "oracle", "_ref", "refgzip")
-    if not os.path.exists(exe):
-        return None
-    n = sample_mib << 20
-    data = gz.corpus(corpus, n).tobytes()
-    best = None
-    for _ in range(2):
+# ---------------------------------------------------------------------------------------------------------------------
+# the reference's own CPU path (oracle/_ref/refgzip = the reference's src/zip.c + src/parallel.c + vendored zlib 1.2.11,
+# unmodified), timed the way BASELINE.md section 3 says: input from a tmpfs file, output to tmpfs, wall clock, best of N
+# ---------------------------------------------------------------------------------------------------------------------
+def scratch_dir():
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    return tempfile.mkdtemp(prefix="gzb_bench_", dir=base)
+
+
+def ref_once(path, level, threads, out_path):
+    cmd = [REFGZIP, f"-{level}"] + (["-j", str(threads)] if threads else [])
+    with open(path, "rb") as fi, open(out_path, "wb") as fo:
         t = time.perf_counter()
-        p = subprocess.run([exe, f"-{level}", "-j", str(threads)], input=data, stdout=subprocess.PIPE)
+        rc = subprocess.run(cmd, stdin=fi, stdout=fo).returncode
         dt = time.perf_counter() - t
-        if p.returncode != 0:
-            return None
-        best = dt if best is None or dt < best else best
-    return {"value": n / best / 1e9, "unit": "GB/s", "cores": threads, "kind": "reference",
-            "sample": f"first {sample_mib} MiB of the {corpus} workload, refgzip -{level} -j {threads}, best of 2, wall clock, output {len(p.stdout)} B",
-            "out_bytes": len(p.stdout), "in_bytes": n}
+    if rc != 0:
+        raise RuntimeError(f"refgzip exited {rc}")
+    return dt, os.path.getsize(out_path)
 
 
-def pick_cpu_sample(level, corpus, threads, target_s=12.0, cap_mib=4096):
-    probe = cpu_reference(level, corpus, 32, threads)
-    if probe is None:
+def cpu_reference(level, corpus, n, threads, tmp, data=None, reps=3, budget_s=16.0, anchors=True):
+    """refgzip -L -j threads on the n bytes of the workload (the SAME bytes the engine compresses: its size is the
+    denominator of size_vs_ref).  Best of `reps` when one run fits the budget, else the one full run."""
+    import gzippier_b200 as gz
+    if not os.path.exists(REFGZIP):
         return None
-    mib = int(min(cap_mib, max(32, probe["value"] * 1e9 * target_s / (1 << 20))))
-    mib = max(32, (mib // 32) * 32)
-    return cpu_reference(level, corpus, mib, threads)
+    path = os.path.join(tmp, f"in_{corpus}_{n}.bin")
+    if not os.path.exists(path):
+        with open(path, "wb") as f:
+            if data is not None:
+                f.write(memoryview(data)[:n])
+            else:
+                step = 1 << 30
+                for off in range(0, n, step):
+                    f.write(memoryview(gz.corpus(corpus, min(step, n - off), offset=off)))
+    outp = os.path.join(tmp, "ref_out.gz")
+    dt, size = ref_once(path, level, threads, outp)
+    times = [dt]
+    while len(times) < reps and min(times) <= budget_s:
+        times.append(ref_once(path, level, threads, outp)[0])
+    best = min(times)
+    res = {"value": round(n / best / 1e9, 4), "unit": "GB/s", "cores": threads, "kind": "reference",
+           "sample": f"the whole {n >> 20} MiB {corpus} workload from a tmpfs file to a tmpfs file, refgzip -{level} -j {threads}, best of {len(times)}, wall clock",
+           "out_bytes": size, "in_bytes": n, "seconds": [round(x, 3) for x in times]}
+    if anchors:
+        # BASELINE configs[0] / BASELINE.md section 3: the single-stream path and -j 1 on 256 MiB of the same corpus, one core each
+        m = min(n, 256 << 20)
+        small = os.path.join(tmp, f"in_{corpus}_{m}.bin")
+        if not os.path.exists(small):
+            with open(path, "rb") as fi, open(small, "wb") as fo:
+                fo.write(fi.read(m))
+        dt1, s1 = ref_once(small, level, 0, outp)
+        # gunzip round trip + CRC32 check of the single-stream member (configs[0])
+        with open(outp, "rb") as f:
+            member = f.read()
+        with open(small, "rb") as f:
+            raw = f.read()
+        back = subprocess.run(["gunzip", "-c"], input=member, stdout=subprocess.PIPE).stdout
+        ok = back == raw and int.from_bytes(member[-8:-4], "little") == zlib.crc32(raw)
+        dtj, sj = ref_once(small, level, 1, outp)
+        res["single_stream"] = {"value": round(m / dt1 / 1e9, 4), "unit": "GB/s", "cores": 1, "in_bytes": m, "out_bytes": s1, "roundtrip_crc_ok": bool(ok),
+                                "what": f"configs[0]: refgzip -{level} (no -j, deflateGZIP single stream) on the first {m >> 20} MiB"}
+        res["j1"] = {"value": round(m / dtj / 1e9, 4), "unit": "GB/s", "cores": 1, "in_bytes": m, "out_bytes": sj, "what": f"refgzip -{level} -j 1 on the first {m >> 20} MiB"}
+    os.unlink(outp)
+    return res
+
+
+def reference_arm(a, cfg, level, corpus, mib, world):
+    """--impl reference: the reference's own CPU implementation of the path on all host threads; maps nothing of the engine."""
+    t0 = time.perf_counter()
+    threads = os.cpu_count() or 1
+    n = mib << 20
+    sample_note = "each step = the whole workload"
+    if cfg == 4:                                     # 64 GiB on the host cores would take minutes per run: bounded sample
+        n = min(n, 4096 << 20); sample_note = "each step = the first 4096 MiB of the 64 GiB workload (bounded sample)"
+    if not os.path.exists(REFGZIP):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/refgzip is not built (run __graft_entry__.build() where /root/reference exists)"}))
+        return 0
+    tmp = scratch_dir()
+    try:
+        res = cpu_reference(level, corpus, n, threads, tmp, reps=max(1, min(a.steps, 3)), anchors=(cfg in (0, 1)))
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    line = {"impl": "reference", "metric": "compress input GB/s", "value": res["value"], "unit": "GB/s", "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": round(n / res["value"] / 1e6, 1), "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(cfg, level, corpus, mib, world), "level": level, "chunk": 131072, "dict": 32768,
+                       "note": "the reference's CPU path (refgzip = its unmodified src/zip.c + src/parallel.c + zlib 1.2.11) on the host cores; " + sample_note},
+            "cpu_baseline": res, "e2e": {"value": res["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": round(time.perf_counter() - t0, 1)}
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# one configuration on this rank's GPU
+# ---------------------------------------------------------------------------------------------------------------------
+class Job:
+    """Input of one rank resident in pinned host memory and in HBM, plus the buffers of both timed paths."""
+
+    def __init__(self, gz, torch, ctx, level, corpus, n, rank, world, final_rank):
+        self.gz, self.torch, self.ctx, self.level, self.corpus, self.n, self.rank, self.world = gz, torch, ctx, level, corpus, n, rank, world
+        self.halo = gz.DICT if rank > 0 else 0
+        # every rank owns the slice [rank*n, (rank+1)*n) of one world*n corpus; the 32 KiB before it is its halo.  The bytes
+        # are generated straight into page-locked memory (no second host copy of a multi-GiB shard).
+        self.pin = torch.empty(n + self.halo, dtype=torch.uint8, pin_memory=True)
+        self.host = self.pin.numpy()
+        gz.corpus(corpus, n + self.halo, offset=rank * n - self.halo, out=self.host)
+        self.d_all = torch.empty(n + self.halo + 32768, dtype=torch.uint8, device="cuda")   # keeps d_in 16-byte aligned after the halo
+        self.d_all[32768 - self.halo: 32768 + n].copy_(self.pin, non_blocking=True)
+        self.d_in = self.d_all[32768:]
+        self.d_out = torch.empty(gz.bound(n), dtype=torch.uint8, device="cuda")
+        self.flags = gz.F_FINAL if final_rank else 0
+        self.stream = torch.cuda.current_stream()
+        torch.cuda.synchronize()
+
+    def step(self):
+        self.ctx.deflate_device_async(self.d_in, self.n, self.d_out, self.level, flags=self.flags, halo=self.halo, stream=self.stream.cuda_stream)
+
+    def shard(self):
+        return self.host[self.halo:]
+
+
+def run_config(gz, torch, dist, ctx, dev, level, corpus, n, rank, world, steps, warmup, full_decode):
+    """-> dict with value / e2e / stage times / parity facts of this rank; collective timing (MAX over ranks) when dist is set."""
+    job = Job(gz, torch, ctx, level, corpus, n, rank, world, final_rank=(rank == world - 1))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(warmup, 3)):
+        job.step(); r = ctx.wait()
+    # ---- correctness gates: a number for a wrong stream is void ----
+    shard = job.shard()
+    assert r.in_bytes == n and r.crc32 == zlib.crc32(memoryview(shard)), "CRC-32 differs from zlib's"
+    # every rank: the device-side round trip of its own shard (k_verify decodes every fragment again and compares it with the
+    # input; also checks the framing: byte-aligned fragments, BFINAL only at the very end).  Raises GzbError(E_VERIFY).
+    rv = ctx.deflate_device(job.d_in, n, job.d_out, level, flags=job.flags | gz.F_VERIFY, halo=job.halo, stream=job.stream.cuda_stream)
+    assert rv.out_bytes == r.out_bytes and rv.crc32 == r.crc32
+    out_bytes = int(r.out_bytes)
+    raw = job.d_out[:out_bytes].cpu().numpy()
+    decoded = "k_verify"
+    if full_decode:                                   # zlib decodes the whole body of this rank (needs the stream to start here)
+        d = zlib.decompressobj(-15, zdict=bytes(job.host[:job.halo])) if job.halo else zlib.decompressobj(-15)
+        pos, piece = 0, 64 << 20
+        mv = memoryview(raw)
+        for off in range(0, out_bytes, piece):
+            got = d.decompress(mv[off: off + piece])
+            assert got == bytes(memoryview(shard)[pos: pos + len(got)]), "zlib round trip differs from the input"
+            pos += len(got)
+        got = d.flush(); assert got == bytes(memoryview(shard)[pos: pos + len(got)]); pos += len(got)
+        assert pos == n, "zlib round trip is short"
+        decoded = "zlib (whole body) + k_verify"
+
+    sampler = ClockSampler(dev); sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage = {k: 0.0 for k in ("crc", "lz77", "huffman", "layout", "pack", "total")}
+    e0.record(job.stream)
+    for _ in range(steps):
+        job.step(); ctx.wait()                       # wait() only syncs this stream; the input (>> L2) is re-read from HBM each step
+        for k, v in ctx.stage_ms().items():
+            stage[k] += v
+    e1.record(job.stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+    clocks = sampler.summary()
+
+    # ---- end to end through the host-buffer entry point: pinned host memory in, pinned host memory out; H2D of the input
+    # and D2H of the compressed bytes are inside the timed region (pipelined with the kernels in batches) ----
+    h_out = torch.empty(out_bytes + (1 << 20), dtype=torch.uint8, pin_memory=True).numpy()   # sized for what comes out, not for gzb_bound
+    hin = job.host[job.halo:]
+    dict_b = job.host[:job.halo] if job.halo else None
+    ctx.deflate_host(hin, level, job.flags, dict_bytes=dict_b, out=h_out)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        body, r2 = ctx.deflate_host(hin, level, job.flags, dict_bytes=dict_b, out=h_out)
+    t_e2e = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([t_e2e], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); t_e2e = float(t.item())
+    assert r2.out_bytes == out_bytes and r2.crc32 == r.crc32
+    assert (body == raw).all(), "the end-to-end path and the device-resident path disagree"          # the bytes just checked above
+    return {"job": job, "raw": raw, "ms": ms, "value": world * n * steps / (ms / 1e3) / 1e9, "e2e": world * n * steps / t_e2e / 1e9,
+            "out_bytes": out_bytes, "crc32": int(r.crc32), "stage": {k: v / steps for k, v in stage.items()}, "clocks": clocks, "decoded": decoded}
+
+
+def size_gate(out_bytes, ref):
+    """engine bytes / reference bytes on the same input at the same level; the contract is <= 1.03 (BASELINE.json)."""
+    if not ref:
+        return None
+    s = out_bytes / (ref["out_bytes"] - 18)          # the reference's member: 10 bytes of header, 8 of trailer
+    assert s <= RATIO_TOL, f"size_vs_ref {s:.4f} > {RATIO_TOL}"
+    return round(s, 5)
+
+
+def check_member(gz, torch, dist, res, tmp, level, n, rank, world, mode):
+    """configs[4]: rank-ordered concatenation into ONE member, CRCs folded by crc32_combine (what write_thread does per job,
+    reference src/parallel.c:510-556).  No collective: every rank drops its body and a small record into a tmpfs
+    directory, rank 0 assembles.  -> dict of facts (rank 0), None elsewhere."""
+    job, raw = res["job"], res["raw"]
+    Z = ctypes.CDLL(REFZ) if os.path.exists(REFZ) else None
+    shard = job.shard()
+    ref_crc = None
+    if Z is not None:                                # CRC of the shard by the REFERENCE's crc32 (lib/zlib/crc32.c), 1 GiB at a time
+        Z.crc32.argtypes = [ctypes.c_ulong, ctypes.c_void_p, ctypes.c_uint]; Z.crc32.restype = ctypes.c_ulong
+        c = 0
+        for off in range(0, n, 1 << 30):
+            c = Z.crc32(c, shard.ctypes.data + off, min(1 << 30, n - off))
+        ref_crc = int(c)
+    with open(os.path.join(tmp, f"part_{rank:02d}"), "wb") as f:
+        f.write(memoryview(raw))
+    # seam: the first fragments of this rank must decode with the last 32 KiB of the PREVIOUS rank's input as dictionary
+    seam_ok = True
+    if rank > 0:
+        d = zlib.decompressobj(-15, zdict=bytes(job.host[:job.halo]))
+        got = d.decompress(bytes(memoryview(raw)[: 8 << 20]))
+        seam_ok = len(got) >= min(n, 1 << 20) and got == bytes(memoryview(shard)[: len(got)])
+    with open(os.path.join(tmp, f"rec_{rank:02d}.json"), "w") as f:
+        json.dump({"n": n, "crc": res["crc32"], "ref_crc": ref_crc, "out_bytes": res["out_bytes"], "seam_ok": bool(seam_ok)}, f)
+    if dist is not None:
+        dist.barrier()
+    if rank != 0:
+        return None
+    recs = [json.load(open(os.path.join(tmp, f"rec_{r:02d}.json"))) for r in range(world)]
+    crc = 0; total = 0
+    for q in recs:
+        crc = gz.crc32_combine(crc, q["crc"], q["n"]); total += q["n"]
+    facts = {"shards": world, "in_bytes": total, "out_bytes": sum(q["out_bytes"] for q in recs) + 18, "crc32": f"{crc:08x}",
+             "seams_decode_ok": all(q["seam_ok"] for q in recs), "mode": mode}
+    if Z is not None:                                # the same fold by the reference's crc32_combine over the reference's CRCs
+        Z.crc32_combine.argtypes = [ctypes.c_ulong, ctypes.c_ulong, ctypes.c_long]; Z.crc32_combine.restype = ctypes.c_ulong
+        rc = 0
+        for q in recs:
+            rc = Z.crc32_combine(rc, q["ref_crc"], q["n"])
+        facts["crc_combined_ok"] = bool(int(rc) == crc)
+    member = os.path.join(tmp, "member.gz")
+    with open(member, "wb") as f:
+        f.write(gz.gzip_header(level))
+        for r in range(world):
+            with open(os.path.join(tmp, f"part_{r:02d}"), "rb") as p:
+                shutil.copyfileobj(p, f, 16 << 20)
+        f.write(gz.gzip_trailer(crc, total))
+    if mode == "full":
+        # the reference's own `gzip -d` and the system's `gunzip -t` must accept the whole member; the decoded stream is
+        # checked by length and CRC (the trailer was written from the engine's fold, the decoder recomputes it from the bytes)
+        t0 = time.perf_counter()
+        tproc = subprocess.Popen(["gunzip", "-t"], stdin=open(member, "rb"), stderr=subprocess.PIPE)
+        ok_ref = None
+        if os.path.exists(REFGZIP):
+            p = subprocess.Popen([REFGZIP, "-d"], stdin=open(member, "rb"), stdout=subprocess.PIPE)
+            c = 0; ln = 0
+            while True:
+                b = p.stdout.read(8 << 20)
+                if not b:
+                    break
+                c = zlib.crc32(b, c); ln += len(b)
+            ok_ref = p.wait() == 0 and ln == total and c == crc
+        ok_t = tproc.wait() == 0
+        facts.update({"refgzip_d_ok": ok_ref, "gunzip_t_ok": bool(ok_t), "decode_seconds": round(time.perf_counter() - t0, 1)})
+        facts["concat_member_ok"] = bool(ok_t and ok_ref is not False and facts["seams_decode_ok"])
+    else:
+        # bounded: zlib decodes the head of the member (header + first shard's start) and the trailer is checked by value
+        head = open(member, "rb").read(8 << 20)
+        d = zlib.decompressobj(31)
+        got = d.decompress(head)
+        tail = open(member, "rb"); tail.seek(-8, 2); tr = tail.read(8)
+        ok = got == bytes(memoryview(job.shard())[: len(got)]) and tr == gz.gzip_trailer(crc, total)
+        facts["concat_member_ok"] = bool(ok and facts["seams_decode_ok"])
+        facts["note"] = "seams + head + trailer decoded here; every fragment of every shard decoded on its GPU by k_verify; --member-check full decodes the whole member with refgzip -d and gunzip -t"
+    assert facts["concat_member_ok"] and facts.get("crc_combined_ok", True), facts
+    return facts
 
 
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     threads = os.cpu_count() or 1
-    workload = f"configs[1]: parallel mode -{a.level}, 128 KiB chunks + 32 KiB dictionary, {a.mib} MiB synthetic {a.corpus} per GPU"
+    cfg = a.config if a.config is not None else (1 if world == 1 and a.gpus == 1 else 4)
+    level = a.level or CONFIGS[cfg]["level"]; corpus = a.corpus or CONFIGS[cfg]["corpus"]
+    mib = a.mib or CONFIGS[cfg]["mib"]
+    if cfg == 4 and a.mib is None:
+        pass                                         # 64 GiB in total, whatever N is
+    nranks = max(world, 1)
+    per_gpu_mib = mib // nranks if cfg == 4 else mib
+    if cfg == 4:
+        per_gpu_mib -= per_gpu_mib % 1               # shards are whole MiB: multiples of the 128 KiB chunk
+    workload = workload_name(cfg, level, corpus, mib if cfg == 4 else per_gpu_mib, nranks if a.impl != "reference" else max(a.gpus, 1))
 
     if a.impl == "reference":
         if rank != 0:
             return 0
-        t0 = time.perf_counter()
-        res = pick_cpu_sample(a.level, a.corpus, threads)
-        if res is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/refgzip is not built (run __graft_entry__.build() where /root/reference exists)"}))
-            return 0
-        line = {"impl": "reference", "metric": "compress input GB/s", "value": round(res["value"], 4), "unit": "GB/s", "n_gpus": a.gpus, "steps": a.steps,
-                "warmup": a.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": workload, "note": "reference CPU path on host cores; each step = the bounded sample below"},
-                "cpu_baseline": res, "e2e": {"value": round(res["value"], 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "gpu_launches": 0, "wall_s": round(time.perf_counter() - t0, 1)}
-        print(json.dumps(line))
-        return 0
+        return reference_arm(a, cfg, level, corpus, mib if cfg == 4 else per_gpu_mib, max(a.gpus, 1))
 
     import torch
     import gzippier_b200 as gz
@@ -124,108 +398,107 @@ def main():
     dev = local if world > 1 else 0
     torch.cuda.set_device(dev)
     ctx = gz.Context(dev)
-    n = a.mib << 20
-    # every rank owns the slice [rank*n, (rank+1)*n) of one world*n corpus; the 32 KiB before it is its halo
-    halo = gz.DICT if rank > 0 else 0
-    host = gz.corpus(a.corpus, n + halo, offset=rank * n - halo)
-    d_all = torch.empty(n + halo + 32768, dtype=torch.uint8, device="cuda")       # keeps d_in 16-byte aligned after the halo
-    d_all[32768 - halo: 32768 + n].copy_(torch.from_numpy(host))
-    d_in = d_all[32768:]
-    d_out = torch.empty(gz.bound(n), dtype=torch.uint8, device="cuda")
-    flags = gz.F_FINAL if rank == world - 1 else 0
-    stream = torch.cuda.current_stream()
+    n = per_gpu_mib << 20
+    tmp = None
+    if rank == 0:
+        tmp = scratch_dir()
+    if dist is not None:
+        box = [tmp]; dist.broadcast_object_list(box, src=0); tmp = box[0]
 
-    def step():
-        ctx.deflate_device_async(d_in, n, d_out, a.level, flags=flags, halo=halo, stream=stream.cuda_stream)
+    try:
+        res = run_config(gz, torch, dist, ctx, dev, level, corpus, n, rank, world, a.steps, a.warmup, full_decode=(world == 1 and n <= (4096 << 20)))
+        member = None
+        if world > 1 or cfg == 4:
+            total = n * world
+            mode = a.member_check if a.member_check != "auto" else ("full" if total <= (8192 << 20) else "seams")
+            if mode != "off":
+                member = check_member(gz, torch, dist, res, tmp, level, n, rank, world, mode)
+        if rank != 0:
+            if dist is not None:
+                dist.barrier(); dist.destroy_process_group()
+            return 0
 
-    def barrier():
-        torch.cuda.synchronize()
+        # ---- rank 0: reference on the host cores, gates, the line ----
+        job = res["job"]
+        cpu = None
+        if not a.no_cpu_baseline:
+            ref_n = n if cfg != 4 else min(n, 4096 << 20)        # configs[4]: bounded sample = the first 4 GiB of the corpus
+            cpu = cpu_reference(level, corpus, ref_n, threads, tmp, data=job.shard(), anchors=(cfg in (0, 1, 4)))
+        size_vs_ref = None
+        if cpu:
+            if cpu["in_bytes"] == n:
+                size_vs_ref = size_gate(res["out_bytes"], cpu)
+            else:                                    # the engine on the same prefix (non-final: the stream goes on)
+                rp = ctx.deflate_device(job.d_in, cpu["in_bytes"], job.d_out, level, flags=0, halo=job.halo, stream=job.stream.cuda_stream)
+                size_vs_ref = size_gate(int(rp.out_bytes), cpu)
+                cpu["sample"] = cpu["sample"].replace("the whole", "the first") + f" (of {n * world >> 20} MiB)"
+
+        others = []
+        if cfg == 1 and world == 1 and not a.no_extra_configs:
+            # the other single-GPU configurations of BASELINE.json, short: 3 steps each, same gates
+            del res["job"], res["raw"]; job = None
+            torch.cuda.empty_cache()
+            for oc in (2, 3):
+                c = CONFIGS[oc]; on = c["mib"] << 20
+                r2 = run_config(gz, torch, None, ctx, dev, c["level"], c["corpus"], on, 0, 1, 3, 3, full_decode=False)
+                ref2 = None if a.no_cpu_baseline else cpu_reference(c["level"], c["corpus"], on, threads, tmp, data=r2["job"].shard(), reps=1, anchors=False)
+                others.append({"config": workload_name(oc, c["level"], c["corpus"], c["mib"], 1), "value": round(r2["value"], 3), "e2e": round(r2["e2e"], 3), "unit": "GB/s",
+                               "steps": 3, "out_bytes": r2["out_bytes"], "ratio": round(on / r2["out_bytes"], 4), "size_vs_ref": size_gate(r2["out_bytes"], ref2),
+                               "reference": None if not ref2 else {"value": ref2["value"], "cores": ref2["cores"], "out_bytes": ref2["out_bytes"], "seconds": ref2["seconds"]},
+                               "roundtrip": r2["decoded"], "stage_ms_per_step": {k: round(v, 3) for k, v in r2["stage"].items()}})
+                del r2; torch.cuda.empty_cache()
+            if cpu and "single_stream" in cpu:
+                # configs[0]: the engine on the anchor's 256 MiB (one member; gunzip round trip + CRC-32)
+                c = CONFIGS[0]; on = c["mib"] << 20
+                d0 = gz.corpus(c["corpus"], on)
+                t0 = time.perf_counter(); m0 = ctx.gzip(d0, c["level"]); dt0 = time.perf_counter() - t0
+                back = subprocess.run(["gunzip", "-c"], input=m0, stdout=subprocess.PIPE).stdout
+                ok = back == d0.tobytes() and int.from_bytes(m0[-8:-4], "little") == zlib.crc32(d0.tobytes())
+                assert ok, "configs[0]: gunzip round trip / CRC-32 failed"
+                others.append({"config": workload_name(0, c["level"], c["corpus"], c["mib"], 1), "engine_member_bytes": len(m0), "engine_wall_s": round(dt0, 3),
+                               "engine_gb_s_from_pageable_memory": round(on / dt0 / 1e9, 3), "gunzip_roundtrip_crc_ok": bool(ok), "reference_single_stream": cpu["single_stream"],
+                               "size_vs_ref_single_stream": round((len(m0) - 18) / (cpu["single_stream"]["out_bytes"] - 18), 5)})
+
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        chunks = -(-n // gz.CHUNK)
+        nsub = -(-chunks // 4096)
+        lz_ms = res["stage"]["lz77"] / min(nsub, 64)                  # average duration of one k_lz77 launch (the context times 64 sub-batches per call)
+        alg_bytes = (n + res["out_bytes"]) / nsub                     # 1 B read + 1/ratio B written per input byte
+        achieved = alg_bytes / (lz_ms / 1e3) / 1e9
+        traffic = None
+        try:
+            prof = json.load(open(os.path.join(ROOT, "profiles", "lz77_traffic.json")))
+            traffic = prof["dram_bytes_per_input_byte"] * n / nsub
+        except (OSError, KeyError, ValueError):
+            pass
+        ms, steps = res["ms"], a.steps
+        line = {"metric": "compress input GB/s", "value": round(res["value"], 3), "unit": "GB/s", "n_gpus": world, "steps": steps, "warmup": max(a.warmup, 3),
+                "ms_per_step": round(ms / steps, 3), "higher_is_better": True, "scaling": "weak" if world == 1 else "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": workload, "level": level, "chunk": gz.CHUNK, "dict": gz.DICT, "in_bytes_per_gpu": n, "out_bytes_rank0": res["out_bytes"],
+                           "ratio": round(n / res["out_bytes"], 4), "size_vs_ref": size_vs_ref, "roundtrip": res["decoded"], "crc32_vs_zlib": "equal",
+                           "l2": f"inputs ({n >> 20} MiB per GPU) larger than L2 (126 MB): no flush needed",
+                           "stage_ms_per_step": {k: round(v, 3) for k, v in res["stage"].items()}},
+                "e2e": {"value": round(res["e2e"], 3), "unit": "GB/s", "h2d_bytes_per_step": n + (gz.DICT if world > 1 else 0), "d2h_bytes_per_step": res["out_bytes"], "steps": steps},
+                "gpu_launches": world * steps * nsub * 5,                    # five kernels per sub-batch of 4096 chunks, on every rank
+                "roofline": {"bound": "hbm", "kernel": "k_lz77", "achieved": round(achieved, 3), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5),
+                             "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                             "note": "integer/latency-bound path: the HBM fraction is small by construction (SURVEY 8d); see profiles/ for issue-slot utilisation"},
+                "cpu_baseline": cpu, "clocks": res["clocks"]}
+        if member:
+            line["config"]["member"] = member
+        if others:
+            line["other_configs"] = others
+        print(json.dumps(line))
         if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(a.warmup, 3)):
-        step(); r = ctx.wait()
-    # correctness gate: a number for a wrong stream is void
-    import zlib
-    raw = d_out[: r.out_bytes].cpu().numpy()
-    if world == 1:
-        assert zlib.decompress(raw.tobytes(), -15) == host.tobytes(), "round trip failed"
-    # every rank: the device-side round trip of its own shard (k_verify; raises GzbError(E_VERIFY) on a mismatch)
-    rv = ctx.deflate_device(d_in, n, d_out, a.level, flags=flags | gz.F_VERIFY, halo=halo, stream=stream.cuda_stream)
-    assert rv.out_bytes == r.out_bytes and rv.crc32 == r.crc32
-    assert r.crc32 == zlib.crc32(host[halo:].tobytes()), "CRC mismatch"
-    out_bytes = r.out_bytes
-
-    sampler = ClockSampler(dev); sampler.start()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage = {k: 0.0 for k in ("crc", "lz77", "huffman", "layout", "pack", "total")}
-    e0.record(stream)
-    for _ in range(a.steps):
-        step(); ctx.wait()                       # wait() only syncs this stream; the input (>> L2) is re-read from HBM each step
-        for k, v in ctx.stage_ms().items():
-            stage[k] += v
-    e1.record(stream)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    if dist is not None:
-        t = torch.tensor([ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
-    clocks = sampler.summary()
-    value = world * n * a.steps / (ms / 1e3) / 1e9
-
-    # end to end through the host-buffer entry point: pinned host memory in, pinned host memory out; H2D of the input
-    # and D2H of the compressed bytes are inside the timed region (pipelined with the kernels in 128 MiB batches)
-    pin_in = torch.from_numpy(host).pin_memory().numpy()
-    h_out = torch.empty(gz.bound(n), dtype=torch.uint8, pin_memory=True).numpy()
-    hin = pin_in[halo:]
-    dict_b = pin_in[:halo] if halo else None
-    e2e_steps = max(1, min(a.steps, 3))
-    ctx.deflate_host(hin, a.level, flags, dict_bytes=dict_b, out=h_out)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        body, r2 = ctx.deflate_host(hin, a.level, flags, dict_bytes=dict_b, out=h_out)
-    t_e2e = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([t_e2e], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); t_e2e = float(t.item())
-    assert r2.out_bytes == out_bytes and r2.crc32 == r.crc32
-    e2e = world * n * e2e_steps / t_e2e / 1e9
-
-    if rank != 0:
-        return 0
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except OSError:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    chunks = -(-n // gz.CHUNK)
-    nsub = -(-chunks // 4096)
-    lz_ms = stage["lz77"] / a.steps / nsub                        # average duration of one k_lz77 launch
-    alg_bytes = (n + out_bytes) / nsub                            # 1 B read + 1/ratio B written per input byte
-    achieved = alg_bytes / (lz_ms / 1e3) / 1e9
-    traffic = None
-    try:
-        prof = json.load(open(os.path.join(ROOT, "profiles", "lz77_traffic.json")))
-        traffic = prof["dram_bytes_per_input_byte"] * n / nsub
-    except (OSError, KeyError, ValueError):
-        pass
-    cpu = None if (a.no_cpu_baseline or world > 1) else pick_cpu_sample(a.level, a.corpus, threads)   # rank 0 at N=1 only
-    line = {"metric": "compress input GB/s", "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-            "ms_per_step": round(ms / a.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": workload, "level": a.level, "chunk": gz.CHUNK, "dict": gz.DICT, "in_bytes_per_gpu": n, "out_bytes_rank0": out_bytes,
-                       "ratio": round(n / out_bytes, 4), "l2": "inputs (4 GiB) larger than L2 (126 MB): no flush needed",
-                       "stage_ms_per_step": {k: round(v / a.steps, 3) for k, v in stage.items()}},
-            "e2e": {"value": round(e2e, 3), "unit": "GB/s", "h2d_bytes_per_step": n + halo, "d2h_bytes_per_step": int(out_bytes), "steps": e2e_steps},
-            "gpu_launches": world * a.steps * nsub * 5,                    # five kernels per sub-batch of 4096 chunks, on every rank
-            "roofline": {"bound": "hbm", "kernel": "k_lz77", "achieved": round(achieved, 3), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5),
-                         "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                         "note": "integer/latency-bound path: the HBM fraction is small by construction (SURVEY 8d); see profiles/ for issue-slot utilisation"},
-            "cpu_baseline": cpu, "clocks": clocks}
-    print(json.dumps(line))
-    if dist is not None:
-        dist.destroy_process_group()
+            dist.barrier(); dist.destroy_process_group()
+    finally:
+        if rank == 0 and tmp:
+            shutil.rmtree(tmp, ignore_errors=True)
     return 0
 
 

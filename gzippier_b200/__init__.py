@@ -9,6 +9,7 @@ import ctypes, os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgzb200.so")
+CORPUS_LIB_PATH = os.path.join(_HERE, "libgzbcorpus.so")     # input generator for bench / tests, separate from the engine
 
 OK, E_ARG, E_LEVEL, E_NOMEM, E_CUDA, E_NO_DEVICE, E_OUT_FULL, E_IO, E_VERIFY = 0, -1, -2, -3, -4, -5, -6, -7, -8
 F_FINAL, F_RSYNCABLE, F_VERIFY = 1, 2, 4
@@ -65,7 +66,6 @@ def lib():
         L.gzb_gzip_header.argtypes = [i32, u32, ctypes.c_char_p, vp, ctypes.c_size_t]
         L.gzb_gzip_trailer.argtypes = [u32, u64, vp, ctypes.c_size_t]
         L.gzb_zip_fd.argtypes = [i32, i32, ctypes.POINTER(ZipOpts)]
-        L.gzb_corpus_fill.argtypes = [i32, u64, u64, vp, u64, i32]
         _lib = L
     return _lib
 
@@ -92,14 +92,25 @@ def gzip_trailer(crc: int, isize: int) -> bytes:
     return buf.raw
 
 
-def corpus(kind: str, n: int, seed: int = 1234, offset: int = 0, threads: int = 0):
-    """n bytes of the named synthetic corpus as a numpy uint8 array (host only)."""
+_corpus_lib = None
+
+
+def corpus(kind: str, n: int, seed: int = 1234, offset: int = 0, threads: int = 0, out=None):
+    """n bytes of the named synthetic corpus as a numpy uint8 array (host only; libgzbcorpus.so, which is not the engine:
+    a process that only calls this maps nothing of libgzb200.so).  `out`: fill this uint8 array instead of a new one."""
+    global _corpus_lib
     import numpy as np
-    out = np.empty(n, dtype=np.uint8)
-    rc = lib().gzb_corpus_fill(CORPUS[kind], seed, offset, out.ctypes.data, n, threads or (os.cpu_count() or 1))
-    if rc != OK:
-        raise GzbError(rc)
-    return out
+    if _corpus_lib is None:
+        C = ctypes.CDLL(CORPUS_LIB_PATH)
+        C.gzb_corpus_fill.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int]
+        _corpus_lib = C
+    if out is None:
+        out = np.empty(n, dtype=np.uint8)
+    assert out.dtype == np.uint8 and out.size >= n and out.flags["C_CONTIGUOUS"]
+    rc = _corpus_lib.gzb_corpus_fill(CORPUS[kind], seed, offset, out.ctypes.data, n, threads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise ValueError(f"gzb_corpus_fill({kind}) failed")
+    return out[:n]
 
 
 class Context:

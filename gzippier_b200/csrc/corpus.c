@@ -20,7 +20,7 @@
  *   GZB_CORPUS_RANDOM  uniform random bytes (incompressible)
  *   GZB_CORPUS_MIXED   1 MiB regions cycling TEXT / BINARY / RANDOM (config 3)
  */
-#include "gzb200.h"
+#include "gzb_corpus.h"
 #include <stdlib.h>
 #include <string.h>
 #include <pthread.h>
@@ -212,20 +212,20 @@ static void *fill_worker(void *arg)
 
 int gzb_corpus_fill(int kind, uint64_t seed, uint64_t offset, uint8_t *dst, uint64_t n, int nthreads)
 {
-    if (kind < GZB_CORPUS_TEXT || kind > GZB_CORPUS_MIXED) return GZB_E_ARG;
-    if (n == 0) return GZB_OK;
-    if (!dst) return GZB_E_ARG;
+    if (kind < GZB_CORPUS_TEXT || kind > GZB_CORPUS_MIXED) return -1;
+    if (n == 0) return 0;
+    if (!dst) return -1;
     pthread_once(&g_once, corpus_init);
     if (nthreads < 1) nthreads = 1;
     if (nthreads > 64) nthreads = 64;
     uint64_t regions = (offset + n - 1) / REGION - offset / REGION + 1;
     if ((uint64_t)nthreads > regions) nthreads = (int)regions;
-    pthread_t th[64]; job_t jobs[64]; int rc = GZB_OK;
+    pthread_t th[64]; job_t jobs[64]; int rc = 0;
     for (int t = 0; t < nthreads; t++) {
         jobs[t] = (job_t){kind, seed, offset, n, dst, t, nthreads};
-        if (t > 0 && pthread_create(&th[t], NULL, fill_worker, &jobs[t]) != 0) { th[t] = 0; if (fill_worker(&jobs[t])) rc = GZB_E_NOMEM; jobs[t].tid = -1; }
+        if (t > 0 && pthread_create(&th[t], NULL, fill_worker, &jobs[t]) != 0) { th[t] = 0; if (fill_worker(&jobs[t])) rc = -1; jobs[t].tid = -1; }
     }
-    if (fill_worker(&jobs[0])) rc = GZB_E_NOMEM;
-    for (int t = 1; t < nthreads; t++) if (jobs[t].tid >= 0) { void *res; pthread_join(th[t], &res); if (res) rc = GZB_E_NOMEM; }
+    if (fill_worker(&jobs[0])) rc = -1;
+    for (int t = 1; t < nthreads; t++) if (jobs[t].tid >= 0) { void *res; pthread_join(th[t], &res); if (res) rc = -1; }
     return rc;
 }

@@ -188,7 +188,7 @@ int gzb_create(int device, gzb_ctx** out)
     ctx->batch_chunks = (uint32_t)env_int("GZB_BATCH_CHUNKS", 1, 1 << 20, 4096);
     ctx->tune.pw = (int)env_int("GZB_PW", 8, 16, 0); if (ctx->tune.pw != 8 && ctx->tune.pw != 16) ctx->tune.pw = 0;
     ctx->tune.help = (int)env_int("GZB_HELP", 0, 3, -1);
-    ctx->tune.rolemap = (int)env_int("GZB_ROLEMAP", 0, 2, -1);
+    ctx->tune.rolemap = (int)env_int("GZB_ROLEMAP", 0, 4, -1);
     ctx->tune.max_run = (int)env_int("GZB_MAX_RUN", 1, 64, 32);
     ctx->tune.force_run = (int)env_int("GZB_FORCE_RUN", 1, 4096, 0);
     ctx->tune.host_batch = (uint64_t)env_int("GZB_HOST_BATCH_MB", 1, 1 << 16, 512) << 20;
@@ -269,7 +269,7 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     const int help = ctx->tune.help >= 0 ? ctx->tune.help : (level >= 7 ? 3 : 0);
     lp.help_ins = help & 1; lp.help_parse = (help >> 1) & 1;
     lp.max_run = ctx->tune.max_run; lp.force_run = ctx->tune.force_run;
-    lz77_role_map(lp, ctx->tune.rolemap >= 0 ? ctx->tune.rolemap : 2);
+    lz77_role_map(lp, ctx->tune.rolemap >= 0 ? ctx->tune.rolemap : 4);
     ctx->n_sub_timed = 0;
 
     CU(ctx, cudaMemsetAsync(ctx->d_cursor, 0, sizeof(Cursor), st));
@@ -292,8 +292,6 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
     if (rc != GZB_OK) return rc;
     const uint64_t nsub = (nchunks64 + sub - 1) / sub;
     if (nsub > 65536) return fail(ctx, GZB_E_ARG, "input too large for one call");
-    // k_pack ORs bits into the output: zero everything that can be written
-    CU(ctx, cudaMemsetAsync(d_out, 0, gzb_bound(n, flags), st));
     CU(ctx, cudaMemsetAsync(ctx->d_work, 0, sizeof(uint32_t) * nsub, st));
 
     for (uint64_t sb = 0; sb < nsub; sb++) {
@@ -528,7 +526,8 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
 {
     if (!ctx || (n && !in) || !out) return GZB_E_ARG;
     if (level < 1 || level > 9) return fail(ctx, GZB_E_LEVEL, "level must be 1..9");
-    if (out_cap < gzb_bound(n, flags)) return fail(ctx, GZB_E_OUT_FULL, "out_cap < gzb_bound(n)");
+    // out_cap >= gzb_bound(n) can never overflow; a smaller buffer is accepted and checked batch by batch (GZB_E_OUT_FULL
+    // before anything is written past it): a caller that knows its ratio need not page-lock n bytes of output
     const bool rs = (flags & GZB_F_RSYNCABLE) != 0;
     const uint32_t dsz = rs ? 0u : GZB_DICT;
     std::lock_guard<std::mutex> g(ctx->mu);

@@ -117,7 +117,11 @@ int gzb_last_stage_ms(gzb_ctx *ctx, gzb_stage_ms *ms);
 /* Compress n bytes of HOST memory into host memory: pinned staging, H2D,
  * kernels, D2H, pipelined in batches of chunks.  `dict` is the 32 KiB that
  * precede `in` in the stream (NULL at the start of the stream).  This is the
- * call the reference-facing host driver makes once per read batch. */
+ * call the reference-facing host driver makes once per read batch.
+ * out_cap >= gzb_bound(n) always suffices; a smaller buffer is accepted and the
+ * call fails with GZB_E_OUT_FULL (nothing written past out_cap) if the output
+ * does not fit.  On any error nothing is left in flight: all copies into the
+ * caller's buffers have completed when the call returns. */
 int gzb_deflate_host(gzb_ctx *ctx, int level, uint32_t flags,
                      const uint8_t *in, uint64_t n, const uint8_t *dict,
                      uint8_t *out, uint64_t out_cap, gzb_result *result);
@@ -171,14 +175,6 @@ void gzb_host_free(void *p);
  * boundary is a multiple of both chunk sizes, and a large input starts with batches of 64, 192 MiB ... and ends with one
  * of <= 64 MiB so that the copies nothing can hide behind stay small (GZB_HOST_BATCH_MB, GZB_HOST_EDGE_MB). */
 int gzb_host_batch_plan(uint64_t n, uint64_t *off, int cap);
-
-/* ---- synthetic corpora for bench/tests (host only, csrc/corpus.c) ---- */
-#define GZB_CORPUS_TEXT    0
-#define GZB_CORPUS_ZIPF    1
-#define GZB_CORPUS_BINARY  2
-#define GZB_CORPUS_RANDOM  3
-#define GZB_CORPUS_MIXED   4
-int gzb_corpus_fill(int kind, uint64_t seed, uint64_t offset, uint8_t *dst, uint64_t n, int nthreads);
 
 #ifdef __cplusplus
 }

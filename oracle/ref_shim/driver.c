@@ -49,6 +49,7 @@ ulg updcrc(const uch *s, unsigned n) { (void)s; (void)n; return 0; } /* decode-s
 void write_buf(int fd, voidp buf, unsigned cnt) { if (write(fd, buf, cnt) != (ssize_t)cnt) write_error(); bytes_out += cnt; }
 void flush_window(void) {}
 int fill_inbuf(int eof_ok, int max_fill) { (void)eof_ok; (void)max_fill; return EOF; }
+char *gzip_base_name(char *fname) { char *p = strrchr(fname, '/'); return p ? p + 1 : fname; }   /* src/util.c; used by the GZIP_B200 seam only */
 
 int main(int argc, char **argv)
 {

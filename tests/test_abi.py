@@ -16,6 +16,10 @@ def test_exports_every_declared_symbol(gz):
     L = ctypes.CDLL(gz.LIB_PATH)
     missing = [n for n in names if not hasattr(L, n)]
     assert not missing, missing
+    # the input generator is a library of its own (include/gzb_corpus.h -> libgzbcorpus.so): the engine does not export it,
+    # and a process that only generates input -- bench.py's reference arm -- maps nothing of the engine
+    assert not hasattr(L, "gzb_corpus_fill") and not hasattr(L, "gzb_test_corrupt_at")
+    assert hasattr(ctypes.CDLL(gz.CORPUS_LIB_PATH), "gzb_corpus_fill")
 
 
 def test_header_cites_reference_for_each_entry_point():

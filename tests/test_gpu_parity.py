@@ -138,6 +138,22 @@ def test_error_codes(gz, ctx):
     assert e.value.code == gz.E_ARG
 
 
+def test_host_call_with_a_smaller_output_buffer(gz, orc, ctx):
+    """gzb_deflate_host accepts out_cap < gzb_bound(n) (a caller that knows its ratio need not page-lock n bytes of output)
+    and reports GZB_E_OUT_FULL instead of writing past it; the context stays usable."""
+    d = gz.corpus("text", 3 * gz.CHUNK + 7, seed=12)
+    want = orc.engine_model(d, 6).tobytes()
+    out = np.empty(len(want) + 100, dtype=np.uint8)
+    raw, r = ctx.deflate_host(d, 6, out=out)
+    assert raw.tobytes() == want
+    guard = np.full(4096, 0x5A, dtype=np.uint8)
+    with pytest.raises(gz.GzbError) as e:
+        ctx.deflate_host(d, 6, out=guard[:1000])
+    assert e.value.code == gz.E_OUT_FULL and (guard[1000:] == 0x5A).all()
+    raw, r = ctx.deflate_host(d, 6, out=out)
+    assert raw.tobytes() == want
+
+
 def test_host_driver_and_cli(gz, orc, tmp_path):
     """gzb_zip_fd / the gzb200 CLI, in the style of the reference's tests/parallel: compress | gzip -d | cmp."""
     exe = os.path.join(os.path.dirname(gz.LIB_PATH), "gzb200")

@@ -8,7 +8,7 @@
 // Question: cycles per tile when the other warps of the CTA are idle / hammer shared memory, and with the three
 // inserters on one scheduler or spread over three.  Results are compared with a sequential CPU insertion.
 #include "gzb_common.cuh"
-#include "gzb200.h"
+#include "gzb_corpus.h"
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>

@@ -7,7 +7,7 @@
 //   every bucket writes it -- no read-back, no votes, so consecutive groups pipeline.
 // Questions: cycles per tile of pass 2 under load; what the MATCH traffic of pass 1 costs the warps that do other work.
 #include "gzb_common.cuh"
-#include "gzb200.h"
+#include "gzb_corpus.h"
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
