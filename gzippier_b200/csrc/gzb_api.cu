@@ -33,6 +33,7 @@ struct Tuning {
     int rolemap = -1;         // GZB_ROLEMAP: warp layout of k_lz77 (-1: by level)
     int max_run = 32;         // GZB_MAX_RUN
     int force_run = 0;        // GZB_FORCE_RUN (tests)
+    int scan = 1;             // GZB_SCAN: 0 = no incompressibility test before the match finder (every chunk takes the normal path)
     uint64_t host_batch = 512ull << 20, host_edge = 64ull << 20;   // GZB_HOST_BATCH_MB, GZB_HOST_EDGE_MB
 };
 
@@ -191,6 +192,7 @@ int gzb_create(int device, gzb_ctx** out)
     ctx->tune.rolemap = (int)env_int("GZB_ROLEMAP", 0, 4, -1);
     ctx->tune.max_run = (int)env_int("GZB_MAX_RUN", 1, 64, 32);
     ctx->tune.force_run = (int)env_int("GZB_FORCE_RUN", 1, 4096, 0);
+    ctx->tune.scan = (int)env_int("GZB_SCAN", 0, 1, 1);
     ctx->tune.host_batch = (uint64_t)env_int("GZB_HOST_BATCH_MB", 1, 1 << 16, 512) << 20;
     ctx->tune.host_edge = (uint64_t)env_int("GZB_HOST_EDGE_MB", 0, 1 << 16, 64) << 20;
     uint32_t tab[CRC_TAB_WORDS];
@@ -304,7 +306,7 @@ int enqueue_deflate(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* d_in
         const bool timed = sb < (uint64_t)MAX_SUB;
         cudaEvent_t* ev = ctx->ev[timed ? sb : 0];
         if (timed) { CU(ctx, cudaEventRecord(ev[0], st)); }
-        launch_crc32(d_in + off, nb, chunk, nch, ctx->scr.chunks, ctx->d_tab, st);
+        launch_scan(d_in + off, nb, h, chunk, dict, nch, bpc, ctx->tune.scan, ctx->scr.chunks, ctx->scr.blocks, ctx->d_tab, st);
         if (timed) { CU(ctx, cudaEventRecord(ev[1], st)); }
         launch_lz77(d_in + off, nb, h, chunk, dict, nch, ctx->scr.tokens, ctx->scr.blocks, ctx->scr.chunks, lp,
                     ctx->d_work + sb, ctx->n_sm, st);
@@ -639,7 +641,7 @@ static int crc32_device_locked(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, 
     for (uint64_t c0 = 0; c0 < nchunks64; c0 += SUB) {
         const uint32_t nch = (uint32_t)((nchunks64 - c0) < SUB ? (nchunks64 - c0) : SUB);
         const uint64_t off = c0 * chunk, nb = (n - off) < (uint64_t)nch * chunk ? (n - off) : (uint64_t)nch * chunk;
-        launch_crc32(d_in + off, nb, chunk, nch, ctx->d_crc_recs, ctx->d_tab, st);
+        launch_scan(d_in + off, nb, 0u, chunk, 0u, nch, 1u, 0, ctx->d_crc_recs, nullptr, ctx->d_tab, st);
         CU(ctx, cudaMemcpyAsync(ctx->h_crc_recs, ctx->d_crc_recs, sizeof(ChunkRec) * nch, cudaMemcpyDeviceToHost, st));
         CU(ctx, cudaStreamSynchronize(st));
         for (uint32_t i = 0; i < nch; i++) {

@@ -77,7 +77,7 @@ struct ChunkRec {
     uint64_t frag_bytes;      // size of the byte-aligned raw-deflate fragment
     uint64_t out_byte;        // absolute byte offset of the fragment in the output buffer
     uint32_t tail_kind;       // 0 none, 1 empty stored block appended for byte alignment
-    uint32_t pad0;
+    uint32_t stored;          // k_scan: the chunk is incompressible -- no match finding, its blocks are stored blocks
     uint64_t tail_bit;        // where the alignment block goes
 };
 
@@ -166,8 +166,38 @@ __host__ __device__ __forceinline__ uint32_t crc_shift(const uint32_t* x2n, uint
 }
 constexpr int CRC_TAB_WORDS = 1024 + 64;      // slice-by-4 tables followed by x^(2^k), k < 64
 
+// ---- incompressibility test of k_scan (the same integer arithmetic as oracle/engine_model.c gzm_chunk_is_stored) ----
+constexpr int      SCAN_MIN        = 4096;    // shorter chunks always take the normal path
+constexpr int      SCAN_SAMPLE     = 256;     // one 16-byte word out of every 256 bytes goes into the byte histogram
+constexpr uint32_t SCAN_MIN_BITS_N = 127, SCAN_MIN_BITS_D = 128;   // "incompressible": order-0 entropy >= 8 * 127/128 bits per byte ...
+constexpr uint32_t SCAN_SLOTS      = 4096;    // ... and fewer than 1 in 64 of the sampled 8-byte grams seen before (table of fingerprints)
+constexpr uint32_t SCAN_MAX_GRAMS  = 3072;
+// 256 * log2(1 + m / 256), rounded
+__device__ __constant__ const uint8_t c_log2_q8[256] = {
+      0,   1,   3,   4,   6,   7,   9,  10,  11,  13,  14,  16,  17,  18,  20,  21,
+     22,  24,  25,  26,  28,  29,  30,  32,  33,  34,  36,  37,  38,  40,  41,  42,
+     44,  45,  46,  47,  49,  50,  51,  52,  54,  55,  56,  57,  59,  60,  61,  62,
+     63,  65,  66,  67,  68,  69,  71,  72,  73,  74,  75,  77,  78,  79,  80,  81,
+     82,  84,  85,  86,  87,  88,  89,  90,  92,  93,  94,  95,  96,  97,  98,  99,
+    100, 102, 103, 104, 105, 106, 107, 108, 109, 110, 111, 112, 113, 114, 116, 117,
+    118, 119, 120, 121, 122, 123, 124, 125, 126, 127, 128, 129, 130, 131, 132, 133,
+    134, 135, 136, 137, 138, 139, 140, 141, 142, 143, 144, 145, 146, 147, 148, 149,
+    150, 151, 152, 153, 154, 155, 155, 156, 157, 158, 159, 160, 161, 162, 163, 164,
+    165, 166, 167, 168, 169, 169, 170, 171, 172, 173, 174, 175, 176, 177, 178, 178,
+    179, 180, 181, 182, 183, 184, 185, 185, 186, 187, 188, 189, 190, 191, 192, 192,
+    193, 194, 195, 196, 197, 198, 198, 199, 200, 201, 202, 203, 203, 204, 205, 206,
+    207, 208, 208, 209, 210, 211, 212, 212, 213, 214, 215, 216, 216, 217, 218, 219,
+    220, 220, 221, 222, 223, 224, 224, 225, 226, 227, 228, 228, 229, 230, 231, 231,
+    232, 233, 234, 234, 235, 236, 237, 238, 238, 239, 240, 241, 241, 242, 243, 244,
+    244, 245, 246, 247, 247, 248, 249, 249, 250, 251, 252, 252, 253, 254, 255, 255};
+// a position is sampled iff the low six bits of its first byte are 0x2A: one in 64 on the near-uniform bytes the test runs on
+__host__ __device__ __forceinline__ uint32_t scan_select(uint32_t w) { return (w & 0x3Fu) == 0x2Au; }
+__host__ __device__ __forceinline__ uint32_t scan_fingerprint(uint32_t w, uint32_t w2) { return ((w * 0x85EBCA6Bu) ^ (w2 * 0xC2B2AE35u)) | 1u; }
+
 // launchers (defined in the k_*.cu files)
-void launch_crc32(const uint8_t* in, uint64_t n_bytes, uint32_t chunk, uint32_t nchunks, ChunkRec* chunks, const uint32_t* d_tab, cudaStream_t st);
+// scan: 0 = CRC-32 only; 1 = CRC-32 + incompressibility test (fills the records of stored chunks); dict / halo as for launch_lz77
+void launch_scan(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks, uint32_t bpc, int scan,
+                 ChunkRec* chunks, BlockRec* blocks, const uint32_t* d_tab, cudaStream_t st);
 void launch_lz77(const uint8_t* in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks,
                  uint32_t* tokens, BlockRec* blocks, ChunkRec* chunks, LevelParams lp, uint32_t* work_ctr, int n_sm, cudaStream_t st);
 void launch_huffman(BlockRec* blocks, const ChunkRec* chunks, uint32_t nchunks, uint32_t bpc, cudaStream_t st);

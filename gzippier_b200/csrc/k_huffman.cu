@@ -207,7 +207,7 @@ k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, ui
     __shared__ HuffSmem S;
     const uint32_t lane = threadIdx.x;
     const uint32_t c = blockIdx.x / bpc, b = blockIdx.x % bpc;
-    if (b >= chunks[c].n_blocks) return;
+    if (b >= chunks[c].n_blocks || chunks[c].stored) return;       // stored chunk (k_scan): its block records are complete
     BlockRec* B = &blocks[blockIdx.x];
 
     for (uint32_t i = lane; i < 288u; i += 32u) S.lfreq[i] = (i < (uint32_t)NLSYM) ? B->lfreq[i] : 0u;

@@ -82,7 +82,7 @@ struct Smem {
     unsigned long long bar_parse[NSTAGE]; // tile's matches consumed by the parser   (1 arrival)
     unsigned long long bar_ctr[NSTAGE];   // the slot's group counter is back to 0   (1 arrival)
     uint32_t gctr[NSTAGE];                // group scheduler of the tile in the slot
-    uint32_t chunk_idx;
+    uint32_t seg_c0, seg_rc;              // the segment (consecutive chunks that are not stored) the CTA works on; seg_rc == 0: no more work
     uint32_t entry;                       // next token start (stream position)
     uint32_t ntok;                        // tokens emitted so far in this chunk
     uint32_t blk;                         // current block index
@@ -631,7 +631,7 @@ __device__ __forceinline__ void search_tile(Smem& S, uint32_t sbase, const Level
 template <int PARSE_WARPS>
 __global__ void __launch_bounds__(LZ_THREADS, 1)
 k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t chunk, uint32_t dict, uint32_t nchunks, uint32_t run,
-       uint32_t* __restrict__ tokens, BlockRec* __restrict__ blocks, ChunkRec* __restrict__ chunks, LevelParams lp,
+       uint32_t* __restrict__ tokens, BlockRec* __restrict__ blocks, ChunkRec* chunks, LevelParams lp,
        uint32_t* __restrict__ work_ctr)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -647,11 +647,28 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
     const uint32_t np = 32u - (uint32_t)__popc(lp.role_mask) + (lp.help_ins ? 3u : 0u) + (lp.help_parse ? (uint32_t)PARSE_WARPS : 0u);
 
     bool fresh = true;                                   // (thread 0) the barrier objects have never been initialised
+    uint32_t cur_c = 0, cur_end = 0;                     // (thread 0) what is left of the run of chunks last taken from the counter
     for (;;) {
-        __syncthreads();                                 // everybody is through with the previous run
+        __syncthreads();                                 // everybody is through with the previous segment
         if (tid == 0) {
-            const uint32_t idx = atomicAdd(work_ctr, 1u);
-            S.chunk_idx = idx;
+            // next SEGMENT: the chunks k_scan marked stored are skipped -- they need neither match finder nor parser -- and
+            // what follows one starts a stream of its own (tables reset, its 32 KiB dictionary inserted again)
+            uint32_t c0s = 0, rcs = 0;
+            for (;;) {
+                if (cur_c >= cur_end) {
+                    const uint32_t idx = atomicAdd(work_ctr, 1u);
+                    if (idx >= nruns) break;
+                    cur_c = idx * run; cur_end = min(cur_c + run, nchunks);
+                }
+                while (cur_c < cur_end && chunks[cur_c].stored) cur_c++;
+                if (cur_c < cur_end) {
+                    c0s = cur_c;
+                    while (cur_c < cur_end && !chunks[cur_c].stored) cur_c++;
+                    rcs = cur_c - c0s;
+                    break;
+                }
+            }
+            S.seg_c0 = c0s; S.seg_rc = rcs;
             for (uint32_t i = 0; i < 5u * (uint32_t)NSTAGE; i++) {               // the five arrays lie back to back
                 const uint32_t a = sbase + (uint32_t)offsetof(Smem, bar_load) + 8u * i;
                 static_assert(offsetof(Smem, bar_ctr) == offsetof(Smem, bar_load) + 4 * 8 * NSTAGE, "barrier arrays are contiguous");
@@ -662,9 +679,9 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
             fresh = false;
             for (uint32_t i = 0; i < (uint32_t)NSTAGE; i++) S.gctr[i] = 0;
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            // the parse enters the run's first chunk right behind its dictionary
-            const uint64_t lo0 = (uint64_t)idx * run * chunk;
-            S.entry = (idx < nruns && dict) ? (uint32_t)min((uint64_t)dict, lo0 + halo) : 0u;
+            // the parse enters the segment's first chunk right behind its dictionary
+            const uint64_t lo0 = (uint64_t)c0s * chunk;
+            S.entry = (rcs && dict) ? (uint32_t)min((uint64_t)dict, lo0 + halo) : 0u;
             S.ntok = 0; S.blk = 0; S.blk_tok0 = 0; S.blk_in0 = 0; S.extra_lit = 0;
             S.carry_pos = NOPOS; S.carry_len = 0; S.carry_dist = 0xFFFFu;
         }
@@ -675,9 +692,9 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
         __syncthreads();
-        if (S.chunk_idx >= nruns) break;
-        const uint32_t c0 = S.chunk_idx * run;                                       // first chunk of the run
-        const uint32_t rc = min(run, nchunks - c0);                                  // chunks in the run
+        if (S.seg_rc == 0u) break;
+        const uint32_t c0 = S.seg_c0;                                                // first chunk of the segment
+        const uint32_t rc = S.seg_rc;                                                // chunks in it
 
         const uint64_t lo = (uint64_t)c0 * chunk;
         const uint32_t nr = (uint32_t)min((uint64_t)rc * chunk, n_bytes - lo);        // bytes of the run

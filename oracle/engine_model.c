@@ -65,6 +65,7 @@ void gzm_level_params(int level, gzm_params *p)
     p->lazy_parse = level >= 4;
     p->maxd = GZM_MAXD; p->hbits = GZM_HBITS; p->block_span = GZM_BLOCK_SPAN;
     p->chunk = 131072; p->dict = 32768; p->use_h3 = 1; p->use_h4 = 1;
+    p->scan = 1;        /* k_scan: incompressible chunks are stored without a search */
     p->good_cut = 0;    /* measured and left off: +0.3..1.1 % bytes for -9 % compare trips per 32-position group */
 }
 
@@ -386,12 +387,90 @@ static void emit_block(bitw *w, const gzm_block_plan *B, const uint8_t *raw, uin
     putbits(w, B->lcode[256], B->llen[256]);
 }
 
+/* ---------------- incompressible chunks (GPU: k_scan) ---------------- */
+/* The decision "store this chunk, do not search it" is taken before the match finder from two order-independent
+ * integer quantities (gzippier_b200/csrc/k_scan.cu computes the same ones in parallel):
+ *   (1) the order-0 entropy, in Q8 fixed point, of one 16-byte word out of every 256 bytes of the chunk must be at
+ *       least 8 * 127/128 bits per byte;
+ *   (2) of the 8-byte grams at content-defined positions (first byte ending in the bits 101010: one in 64 on near-uniform bytes) of the chunk,
+ *       fewer than 1 in 64 may equal a gram seen before in the chunk or in its dictionary.
+ * zlib takes the same decision after the search (_tr_flush_block, lib/zlib/trees.c:945-993). */
+static const uint8_t k_log2_q8[256] = {
+      0,   1,   3,   4,   6,   7,   9,  10,  11,  13,  14,  16,  17,  18,  20,  21,
+     22,  24,  25,  26,  28,  29,  30,  32,  33,  34,  36,  37,  38,  40,  41,  42,
+     44,  45,  46,  47,  49,  50,  51,  52,  54,  55,  56,  57,  59,  60,  61,  62,
+     63,  65,  66,  67,  68,  69,  71,  72,  73,  74,  75,  77,  78,  79,  80,  81,
+     82,  84,  85,  86,  87,  88,  89,  90,  92,  93,  94,  95,  96,  97,  98,  99,
+    100, 102, 103, 104, 105, 106, 107, 108, 109, 110, 111, 112, 113, 114, 116, 117,
+    118, 119, 120, 121, 122, 123, 124, 125, 126, 127, 128, 129, 130, 131, 132, 133,
+    134, 135, 136, 137, 138, 139, 140, 141, 142, 143, 144, 145, 146, 147, 148, 149,
+    150, 151, 152, 153, 154, 155, 155, 156, 157, 158, 159, 160, 161, 162, 163, 164,
+    165, 166, 167, 168, 169, 169, 170, 171, 172, 173, 174, 175, 176, 177, 178, 178,
+    179, 180, 181, 182, 183, 184, 185, 185, 186, 187, 188, 189, 190, 191, 192, 192,
+    193, 194, 195, 196, 197, 198, 198, 199, 200, 201, 202, 203, 203, 204, 205, 206,
+    207, 208, 208, 209, 210, 211, 212, 212, 213, 214, 215, 216, 216, 217, 218, 219,
+    220, 220, 221, 222, 223, 224, 224, 225, 226, 227, 228, 228, 229, 230, 231, 231,
+    232, 233, 234, 234, 235, 236, 237, 238, 238, 239, 240, 241, 241, 242, 243, 244,
+    244, 245, 246, 247, 247, 248, 249, 249, 250, 251, 252, 252, 253, 254, 255, 255};
+static uint32_t lg_q8(uint32_t x)      /* 256 * log2(x), x >= 1 */
+{
+    uint32_t k = 31u - (uint32_t)__builtin_clz(x);
+    uint32_t m = k >= 8u ? (x >> (k - 8u)) & 0xFFu : (x << (8u - k)) & 0xFFu;
+    return (k << 8) + k_log2_q8[m];
+}
+int gzm_chunk_is_stored(const uint8_t *s, int D, int n)
+{
+    if (n < GZM_SCAN_MIN) return 0;
+    const uint8_t *c = s + D;
+    uint32_t h[256]; memset(h, 0, sizeof(h));
+    uint32_t ns = 0;
+    for (int o = 0; o + 16 <= n; o += GZM_SCAN_SAMPLE) { for (int k = 0; k < 16; k++) h[c[o + k]]++; ns += 16; }
+    uint64_t bits = 0;
+    for (int b = 0; b < 256; b++) if (h[b]) bits += (uint64_t)h[b] * (lg_q8(ns) - lg_q8(h[b]));
+    if (bits * 128u < (uint64_t)ns * 8u * 256u * 127u) return 0;
+    uint32_t *tab = (uint32_t *)calloc(GZM_SCAN_SLOTS, sizeof(uint32_t));
+    uint32_t distinct = 0, grams = 0, fresh = 0;
+    int P = ((D + n) / 4 - 2) * 4, overflow = 0;            /* positions whose three aligned words lie inside the stream */
+    for (int p = 0; p < P && !overflow; p++) {
+        if (p >= D || p < (D < P ? D : P)) {
+            uint32_t a = ld32(s + p), b = ld32(s + p + 4);
+            if ((a & 0x3Fu) != 0x2Au) continue;             /* sampled positions: first byte ends in 101010 */
+            uint32_t fp = ((a * 0x85EBCA6Bu) ^ (b * 0xC2B2AE35u)) | 1u, slot = (fp >> 8) & (GZM_SCAN_SLOTS - 1);
+            int isnew = 0;
+            for (;;) {
+                if (tab[slot] == fp) break;
+                if (tab[slot] == 0) { tab[slot] = fp; isnew = 1; break; }
+                slot = (slot + 1) & (GZM_SCAN_SLOTS - 1);
+            }
+            if (isnew && ++distinct > GZM_SCAN_MAX_GRAMS) overflow = 1;
+            if (p >= D) { grams++; fresh += (uint32_t)isnew; }
+        }
+    }
+    free(tab);
+    if (overflow || grams == 0) return 0;
+    return (grams - fresh) * 64u < grams;
+}
+
 /* ---------------- one chunk ---------------- */
 size_t gzm_deflate_chunk(const gzm_params *P, const uint8_t *stream, int D, int n_chunk, int final,
                          uint8_t *out, gzm_chunk_stats *st)
 {
     int n = n_chunk;
     const uint8_t *chunk = stream + D;
+    if (P->scan && gzm_chunk_is_stored(stream, D, n)) {
+        /* stored without a search: blocks are the plain 64 KiB spans of the chunk */
+        bitw w = {out, 0};
+        gzm_block_plan B; memset(&B, 0, sizeof(B));
+        int nblocks = (n + P->block_span - 1) / P->block_span;
+        for (int b = 0; b < nblocks; b++) {
+            uint32_t lo = (uint32_t)b * (uint32_t)P->block_span, hi = lo + (uint32_t)P->block_span < (uint32_t)n ? lo + (uint32_t)P->block_span : (uint32_t)n;
+            emit_block(&w, &B, chunk + lo, hi - lo, NULL, 0, final && b == nblocks - 1);
+            if (st) st->blocks[0]++;
+        }
+        if (final) { while (w.bitpos & 7) putbits(&w, 0, 1); }
+        else if (w.bitpos & 7) { putbits(&w, 0, 3); while (w.bitpos & 7) putbits(&w, 0, 1); putbits(&w, 0, 16); putbits(&w, 0xffff, 16); }
+        return (size_t)(w.bitpos >> 3);
+    }
     uint16_t *mlen = (uint16_t *)malloc(sizeof(uint16_t) * (size_t)(n + 1));
     uint16_t *mdist = (uint16_t *)malloc(sizeof(uint16_t) * (size_t)(n + 1));
     uint32_t *tok = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(n + 1));

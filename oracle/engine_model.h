@@ -10,6 +10,10 @@ extern "C" {
 #define GZM_HBITS       14
 #define GZM_H3BITS      12                        /* single-entry table of most recent 3-byte twins */
 #define GZM_H4BITS      12                        /* single-entry table of most recent 4-byte twins */
+#define GZM_SCAN_MIN    4096                      /* k_scan: shorter chunks always take the normal path       */
+#define GZM_SCAN_SAMPLE 256                       /* one 16-byte word per 256 bytes goes into the histogram   */
+#define GZM_SCAN_SLOTS  4096
+#define GZM_SCAN_MAX_GRAMS 3072
 #define GZM_WALK_STEPS  4                         /* chain steps per round of the walk (k_lz77 search_group)  */
 #define GZM_TILE        2048                      /* positions per pipeline step of the LZ77 kernel */
 #define GZM_MAXD        32768                     /* farthest match (the link ring is 32768+2*TILE) */
@@ -23,6 +27,7 @@ typedef struct gzm_params {
     int maxd, hbits, block_span, chunk, dict;
     int use_h3;                                   /* fall back to the most recent 3-byte twin when nothing longer exists */
     int use_h4;                                   /* ... and to the most recent 4-byte twin when the chain gives < 6  */
+    int scan;                                     /* 1: incompressible chunks are stored without a search (k_scan)   */
     int good_cut;                                 /* quarter the remaining candidate budget once the best match reaches `good` */
 } gzm_params;
 
@@ -43,6 +48,7 @@ uint32_t gzm_hash4(uint32_t v);
 uint32_t gzm_hash3(uint32_t v);
 int      gzm_len_code(int len);
 int      gzm_dist_code(int dist);
+int      gzm_chunk_is_stored(const uint8_t *stream, int D, int n_chunk);
 void     gzm_find_matches(const gzm_params *P, const uint8_t *stream, int D, int n, uint16_t *mlen, uint16_t *mdist);
 int      gzm_parse(const gzm_params *P, const uint8_t *chunk, int n, const uint16_t *mlen, const uint16_t *mdist,
                    uint32_t *tokens, uint32_t *tok_pos);

@@ -83,7 +83,7 @@ def inflate(raw, out_cap, stats=None):
 
 
 class ModelParams(ctypes.Structure):
-    _fields_ = [(k, ctypes.c_int) for k in "level good max_lazy nice ref_chain depth lazy_parse maxd hbits block_span chunk dict use_h3 use_h4 good_cut".split()]
+    _fields_ = [(k, ctypes.c_int) for k in "level good max_lazy nice ref_chain depth lazy_parse maxd hbits block_span chunk dict use_h3 use_h4 scan good_cut".split()]
 
 
 def engine_model(data, level, halo=0, final=True, rsyncable=False, threads=8, skip=0):

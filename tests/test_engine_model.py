@@ -62,3 +62,21 @@ def test_model_static_blocks_with_high_literals(gz, orc):
         d = gz.corpus("random", n, seed=9)
         raw = orc.engine_model(d, 6)
         assert zlib.decompress(raw.tobytes(), -15) == d.tobytes()
+
+
+def test_model_stored_decision(gz, orc):
+    """gzm_chunk_is_stored (the CPU statement of k_scan's test): random and already-compressed data are stored without a
+    search; text, base64 and flat-but-repetitive data are not."""
+    import base64, ctypes
+    import numpy as np
+    L = orc.lib(); L.gzm_chunk_is_stored.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+    f = lambda d, D=0: L.gzm_chunk_is_stored(d.ctypes.data, D, d.size - D)
+    rnd = gz.corpus("random", 131072 + 32768, seed=1)
+    assert f(rnd, 32768) == 1 and f(rnd[:131072].copy()) == 1
+    assert f(gz.corpus("text", 131072)) == 0 and f(gz.corpus("binary", 131072)) == 0 and f(gz.corpus("zipf", 131072)) == 0
+    z = np.frombuffer(zlib.compress(gz.corpus("text", 1 << 20).tobytes(), 9)[:131072], dtype=np.uint8).copy()
+    assert f(z) == 1
+    assert f(np.concatenate([rnd[:16384]] * 8)) == 0                                   # the same 16 KiB eight times
+    assert f(np.concatenate([rnd[:32768], rnd[:32768], gz.corpus("random", 98304, seed=7)]), 32768) == 0   # starts with a copy of its dictionary
+    assert f(np.frombuffer(base64.b64encode(rnd[:98304].tobytes()), dtype=np.uint8).copy()) == 0
+    assert f(rnd[:4095].copy()) == 0                                                   # below SCAN_MIN: always the normal path

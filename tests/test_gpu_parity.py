@@ -138,6 +138,35 @@ def test_error_codes(gz, ctx):
     assert e.value.code == gz.E_ARG
 
 
+def test_incompressible_chunks_are_stored_without_a_search(gz, orc, ctx, monkeypatch):
+    """k_scan decides "stored" per chunk BEFORE the match finder (flat byte histogram and no repeated 8-byte grams);
+    the model takes the same decision from the same integers.  Flat but repetitive data must still be searched."""
+    rnd = gz.corpus("random", 5 * gz.CHUNK + 4321, seed=33)
+    rep = np.concatenate([rnd[:16384]] * 24 + [rnd[:777]])                          # random, but every 16 KiB the same
+    z = np.frombuffer(zlib.compress(gz.corpus("text", 3 << 20, seed=34).tobytes(), 9), dtype=np.uint8).copy()   # deflate output: flat, no repeats
+    mix = np.concatenate([gz.corpus("text", 2 * gz.CHUNK, seed=35), rnd[: 2 * gz.CHUNK], gz.corpus("binary", gz.CHUNK + 5, seed=36), rnd[: gz.CHUNK + 1]])
+    for d in (rnd, rep, z, mix):
+        for level in (1, 6, 9):
+            raw, r = ctx.deflate_host(d, level, gz.F_FINAL | gz.F_VERIFY)
+            check_member(gz, orc, d, raw, r, level)
+            assert raw.tobytes() == orc.engine_model(d, level).tobytes()
+    raw, r = ctx.deflate_host(rnd, 6)
+    assert raw.size <= rnd.size + 20 * (rnd.size // gz.CHUNK + 1)                      # all stored
+    raw, r = ctx.deflate_host(rep, 6)
+    assert raw.size < rep.size // 10                                                   # searched: the repeats are found
+    # with the test switched off every chunk takes the normal path: same data back, size within a few bytes per block
+    monkeypatch.setenv("GZB_SCAN", "0")
+    c = gz.Context(0)
+    try:
+        for d in (rnd, mix):
+            raw0, r0 = c.deflate_host(d, 6, gz.F_FINAL | gz.F_VERIFY)
+            assert zlib.decompress(raw0.tobytes(), -15) == d.tobytes()
+            raw1, _ = ctx.deflate_host(d, 6)
+            assert abs(int(raw0.size) - int(raw1.size)) <= 64 * (d.size // gz.CHUNK + 1)
+    finally:
+        c.close()
+
+
 def test_host_call_with_a_smaller_output_buffer(gz, orc, ctx):
     """gzb_deflate_host accepts out_cap < gzb_bound(n) (a caller that knows its ratio need not page-lock n bytes of output)
     and reports GZB_E_OUT_FULL instead of writing past it; the context stays usable."""

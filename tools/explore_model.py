@@ -8,7 +8,7 @@ subprocess.check_call(f"gcc -O2 -shared -fPIC -I{ROOT}/include -o /tmp/libcorpus
 C = ctypes.CDLL('/tmp/libcorpus.so'); M = ctypes.CDLL('/tmp/libmodel.so')
 C.gzb_corpus_fill.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int]
 class Params(ctypes.Structure):
-    _fields_ = [(k, ctypes.c_int) for k in "level good max_lazy nice ref_chain depth lazy_parse maxd hbits block_span chunk dict use_h3 use_h4 good_cut".split()]
+    _fields_ = [(k, ctypes.c_int) for k in "level good max_lazy nice ref_chain depth lazy_parse maxd hbits block_span chunk dict use_h3 use_h4 scan good_cut".split()]
 class Stats(ctypes.Structure):
     _fields_ = [("tokens", ctypes.c_uint64), ("matches", ctypes.c_uint64), ("blocks", ctypes.c_uint64 * 3)]
 M.gzm_deflate.restype = ctypes.c_int64

@@ -7,7 +7,7 @@ import gzippier_b200 as gz
 subprocess.check_call(f"gcc -O2 -shared -fPIC -o /tmp/libmodel.so {ROOT}/oracle/engine_model.c -lpthread", shell=True)
 M = ctypes.CDLL('/tmp/libmodel.so')
 class Params(ctypes.Structure):
-    _fields_ = [(k, ctypes.c_int) for k in "level good max_lazy nice ref_chain depth lazy_parse maxd hbits block_span chunk dict use_h3 use_h4 good_cut".split()]
+    _fields_ = [(k, ctypes.c_int) for k in "level good max_lazy nice ref_chain depth lazy_parse maxd hbits block_span chunk dict use_h3 use_h4 scan good_cut".split()]
 M.gzm_deflate.restype = ctypes.c_int64
 M.gzm_deflate.argtypes = [ctypes.POINTER(Params), ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_void_p]
 def model(data, level):
