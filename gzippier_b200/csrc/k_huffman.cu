@@ -168,26 +168,58 @@ __device__ void huff_codes(const uint8_t* lens, int nsym, int maxbits, uint16_t*
     for (int c = 0; c < NCH; c++) { const uint32_t i = (uint32_t)c * 32u + lane; if (i < (uint32_t)nsym) codes[i] = (uint16_t)cod[c]; }
 }
 
-// RLE of code lengths (scan_tree/send_tree, trees.c:703-793); lane 0 only
-__device__ int rle_lengths(const uint8_t* lens, int n, uint8_t* sym, uint8_t* ext)
+// Run-length coding of a code-length sequence with the symbols 16 / 17 / 18 (RFC 1951 3.2.7), the engine's own policy
+// (oracle/engine_model.c rle_lengths states it sequentially; zlib's is scan_tree / send_tree, lib/zlib/trees.c:703-793):
+// the sequence is cut into MAXIMAL runs of equal lengths and every run is coded on its own --
+//   zeros:  as many "18" (138 zeros) as fit, then one "18" / "17" for 3 or more left over, else the zeros themselves;
+//   v != 0: v once, then "16" (repeat 3..6) while 3 or more are left, else one or two plain v.
+// Whole warp: run starts by ballot, ONE LANE PER RUN computes how many symbols its run takes, a warp scan turns the
+// counts into offsets, and every lane writes its run's symbols.  Returns the number of symbols.
+__device__ __forceinline__ int rle_run_count(int v, int L)
 {
-    int k = 0, prevlen = -1, curlen, nextlen = lens[0], count = 0, max_count = 7, min_count = 4;
-    if (nextlen == 0) { max_count = 138; min_count = 3; }
-    for (int i = 0; i < n; i++) {
-        curlen = nextlen; nextlen = (i + 1 < n) ? lens[i + 1] : 0xffff;
-        if (++count < max_count && curlen == nextlen) continue;
-        else if (count < min_count) { while (count--) { sym[k] = (uint8_t)curlen; ext[k++] = 0; } }
-        else if (curlen != 0) {
-            if (curlen != prevlen) { sym[k] = (uint8_t)curlen; ext[k++] = 0; count--; }
-            sym[k] = 16; ext[k++] = (uint8_t)(count - 3);
-        } else if (count <= 10) { sym[k] = 17; ext[k++] = (uint8_t)(count - 3); }
-        else { sym[k] = 18; ext[k++] = (uint8_t)(count - 11); }
-        count = 0; prevlen = curlen;
-        if (nextlen == 0) { max_count = 138; min_count = 3; }
-        else if (curlen == nextlen) { max_count = 6; min_count = 3; }
-        else { max_count = 7; min_count = 4; }
+    if (v == 0) { const int q = L / 138, r = L % 138; return q + (r >= 3 ? 1 : r); }
+    const int R = L - 1, q = R / 6, r = R % 6;
+    return 1 + q + (r >= 3 ? 1 : r);
+}
+__device__ int rle_lengths(HuffSmem& S, const uint8_t* lens, int n, uint8_t* sym, uint8_t* ext, uint32_t lane)
+{
+    uint16_t* runpos = reinterpret_cast<uint16_t*>(S.key);        // start position of every run (S.key is free here)
+    // 1. run starts: position i starts a run iff i == 0 or lens[i] != lens[i - 1]
+    int nruns = 0;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + (int)lane;
+        const bool start = i < n && (i == 0 || lens[i] != lens[i - 1]);
+        const uint32_t m = __ballot_sync(FULL, start);
+        if (start) runpos[nruns + __popc(m & ((1u << lane) - 1u))] = (uint16_t)i;
+        nruns += __popc(m);
     }
-    return k;
+    if (lane == 0) runpos[nruns] = (uint16_t)n;
+    __syncwarp();
+    // 2. one lane per run: symbols needed, offsets by a warp scan (runs in rounds of 32), then the symbols
+    int total = 0;
+    for (int r0 = 0; r0 < nruns; r0 += 32) {
+        const int r = r0 + (int)lane;
+        int v = 0, L = 0, cnt = 0;
+        if (r < nruns) { const int i = runpos[r]; v = lens[i]; L = (int)runpos[r + 1] - i; cnt = rle_run_count(v, L); }
+        int incl = cnt;
+        for (int o = 1; o < 32; o <<= 1) { const int x = __shfl_up_sync(FULL, incl, o); if ((int)lane >= o) incl += x; }
+        int k = total + incl - cnt;
+        if (v == 0) {
+            while (L >= 138) { sym[k] = 18; ext[k++] = 138 - 11; L -= 138; }
+            if (L >= 11) { sym[k] = 18; ext[k++] = (uint8_t)(L - 11); }
+            else if (L >= 3) { sym[k] = 17; ext[k++] = (uint8_t)(L - 3); }
+            else while (L-- > 0) { sym[k] = 0; ext[k++] = 0; }
+        } else {
+            sym[k] = (uint8_t)v; ext[k++] = 0;
+            int R = L - 1;
+            while (R >= 6) { sym[k] = 16; ext[k++] = 6 - 3; R -= 6; }
+            if (R >= 3) { sym[k] = 16; ext[k++] = (uint8_t)(R - 3); }
+            else while (R-- > 0) { sym[k] = (uint8_t)v; ext[k++] = 0; }
+        }
+        total += __shfl_sync(FULL, incl, 31);
+    }
+    __syncwarp();
+    return total;
 }
 
 // LSB-first bit writer: bits collect in a 64-bit accumulator and leave a byte at a time
@@ -221,16 +253,12 @@ k_huffman(BlockRec* __restrict__ blocks, const ChunkRec* __restrict__ chunks, ui
     if (maxl < 256) maxl = 256;
     const int hlit = maxl + 1, hdist = maxd + 1;
 
-    // code-length alphabet
-    int nrle = 0;
-    if (lane == 0) {
-        int k1 = rle_lengths(S.llen, hlit, S.rsym, S.rext);
-        int k2 = rle_lengths(S.dlen, hdist, S.rsym + k1, S.rext + k1);
-        nrle = k1 + k2;
-        for (int i = 0; i < 19; i++) S.bfreq[i] = 0;
-        for (int i = 0; i < nrle; i++) S.bfreq[S.rsym[i]]++;
-    }
-    nrle = __shfl_sync(FULL, nrle, 0);
+    // code-length alphabet: run-length code of the two length sequences (whole warp), histogram of its symbols
+    const int k1 = rle_lengths(S, S.llen, hlit, S.rsym, S.rext, lane);
+    const int nrle = k1 + rle_lengths(S, S.dlen, hdist, S.rsym + k1, S.rext + k1, lane);
+    if (lane < 19u) S.bfreq[lane] = 0;
+    __syncwarp();
+    for (int i = (int)lane; i < nrle; i += 32) atomicAdd(&S.bfreq[S.rsym[i]], 1u);
     __syncwarp();
     huff_lengths<true>(S, S.bfreq, 19, 7, S.blen, lane);
     huff_codes<1>(S.blen, 19, 7, S.bcode, lane);

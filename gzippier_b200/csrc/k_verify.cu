@@ -13,8 +13,11 @@
 // and checks the framing the reference's decoder relies on: BFINAL only on the last block of the last chunk,
 // fragments byte-aligned and exactly frag_bytes long, every chunk decoding to exactly its n_bytes.
 //
-// One warp per chunk: lane 0 runs the bit-serial canonical decoder (tables in shared memory, built per block from the
-// code lengths in the stream, not from BlockRec); the 32 lanes compare match and stored bytes together.
+// One warp per chunk.  The code tables are built by the whole warp, per block, from the code lengths IN THE STREAM (not
+// from BlockRec): a canonical prefix code (RFC 1951 3.2.2) is kept as its codes in ascending order, left-justified to
+// 15 bits, with the symbol and length beside each; decoding a symbol is then "take the next 15 bits most significant
+// first, find the last entry that is not greater" -- a binary search, no bit-serial walk.  Lane 0 owns the bit reader;
+// the 32 lanes compare match and stored bytes together.
 #include "gzb_common.cuh"
 
 namespace gzb {
@@ -24,8 +27,10 @@ namespace {
 constexpr int VERIFY_WARPS = 8;
 constexpr uint32_t FULLM = 0xFFFFFFFFu;
 
-struct Huff { uint16_t count[16]; uint16_t symbol[288]; };
-struct WarpTabs { Huff lit, dist; uint8_t lens[320]; };
+// A canonical prefix code in decode order: entry i has the i-th smallest code; lj[i] = that code, most significant bit
+// first, shifted up to 15 bits; ent[i] = symbol | length << 12.  (Codes sorted by (length, symbol) ascend when left-justified.)
+struct Code { uint16_t* lj; uint16_t* ent; int n; };
+struct WarpTabs { uint16_t lit_lj[288], lit_ent[288], dst_lj[32], dst_ent[32], aux_lj[32], aux_ent[32]; uint8_t lens[320]; uint8_t cl[32]; };
 
 struct Bits {
     const uint8_t* p; uint64_t nbytes; uint64_t byte; uint64_t buf; int have; int err;
@@ -48,31 +53,51 @@ __device__ __forceinline__ uint32_t take(Bits& b, int n)   // n <= 16; LSB first
 }
 __device__ __forceinline__ uint64_t consumed_bits(const Bits& b) { return b.byte * 8ull - (uint64_t)b.have; }
 
-// canonical code from lengths (RFC 1951 3.2.2): <0 over-subscribed, >0 incomplete, 0 complete
-__device__ int build(Huff& h, const uint8_t* len, int n)
+// Whole warp: the code for lens[0, n) (n <= 288).  Returns the Kraft balance: 0 complete, > 0 incomplete (code space left,
+// in units of 2^-15), < 0 over-subscribed (no table is built).  Symbols of one length are ranked with ballots, as k_huffman
+// assigns its codes.
+__device__ int build_code(Code& c, const uint8_t* lens, int n, uint32_t lane)
 {
-    uint16_t offs[16];
-    for (int i = 0; i < 16; i++) h.count[i] = 0;
-    for (int i = 0; i < n; i++) h.count[len[i]]++;
-    int left = 1;
-    for (int l = 1; l <= 15; l++) { left <<= 1; left -= h.count[l]; if (left < 0) return left; }
-    offs[1] = 0;
-    for (int l = 1; l < 15; l++) offs[l + 1] = (uint16_t)(offs[l] + h.count[l]);
-    for (int i = 0; i < n; i++) if (len[i]) h.symbol[offs[len[i]]++] = (uint16_t)i;
-    return left;
+    uint32_t len[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) { const int i = k * 32 + (int)lane; len[k] = i < n ? lens[i] : 0u; }
+    const uint32_t lt = (1u << lane) - 1u;
+    int used = 0, kraft = 0;
+    uint32_t code = 0;                              // first code of the current length, as a number of that many bits
+    for (uint32_t l = 1; l <= 15u; l++) {
+        code <<= 1;
+        uint32_t cnt = 0;
+#pragma unroll
+        for (int k = 0; k < 9; k++) {
+            const uint32_t m = __ballot_sync(FULLM, len[k] == l);
+            if (len[k] == l && kraft >= 0) {
+                const uint32_t r = cnt + (uint32_t)__popc(m & lt);
+                c.lj[used + r] = (uint16_t)((code + r) << (15u - l));
+                c.ent[used + r] = (uint16_t)((uint32_t)(k * 32 + (int)lane) | (l << 12));
+            }
+            cnt += (uint32_t)__popc(m);
+        }
+        kraft += (int)(cnt << (15u - l));
+        if (kraft > (1 << 15)) kraft = -1;           // over-subscribed: stop filling (the entries would overflow the table)
+        if (kraft < 0) break;
+        used += (int)cnt; code += cnt;
+    }
+    c.n = used;
+    __syncwarp();
+    return kraft < 0 ? -1 : (1 << 15) - kraft;
 }
-__device__ int decode(Bits& b, const Huff& h)      // Huffman codes are packed starting with their MSB
+// lane 0: next symbol, or -1 if the bits are no code of c
+__device__ int decode_sym(Bits& b, const Code& c)
 {
     if (b.have < 15) refill(b);
-    int code = 0, first = 0, index = 0;
-    uint64_t buf = b.buf;
-    for (int l = 1; l <= 15; l++) {
-        code |= (int)(buf & 1ull); buf >>= 1;
-        const int count = h.count[l];
-        if (code - count < first) { b.buf = buf; b.have -= l; return h.symbol[index + (code - first)]; }
-        index += count; first += count; first <<= 1; code <<= 1;
-    }
-    return -1;
+    if (c.n == 0) return -1;
+    const uint32_t x = __brev((uint32_t)b.buf) >> 17;          // the next 15 bits, first bit most significant
+    int lo = 0, hi = c.n - 1;                                  // the last entry with lj <= x (lj[0] == 0)
+    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (c.lj[mid] <= x) lo = mid; else hi = mid - 1; }
+    const uint32_t e = c.ent[lo], l = e >> 12;
+    if ((x ^ c.lj[lo]) >> (15u - l)) return -1;                // only in an incomplete code: bits past the last code
+    b.buf >>= l; b.have -= (int)l;
+    return (int)(e & 0xFFFu);
 }
 
 __constant__ uint16_t c_lbase[29] = {3,4,5,6,7,8,9,10,11,13,15,17,19,23,27,31,35,43,51,59,67,83,99,115,131,163,195,227,258};
@@ -139,23 +164,32 @@ k_verify(const uint8_t* __restrict__ in, uint32_t chunk, uint32_t dict, uint32_t
         }
         // code tables of the block
         uint32_t e = 0;
-        if (lane == 0) {
-            if (type == 1u) {
-                for (int i = 0; i < 288; i++) T.lens[i] = (uint8_t)(i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8);
-                build(T.lit, T.lens, 288);
-                for (int i = 0; i < 30; i++) T.lens[i] = 5;
-                build(T.dist, T.lens, 30);
-            } else {
-                const int hlit = (int)take(b, 5) + 257, hdist = (int)take(b, 5) + 1, hclen = (int)take(b, 4) + 4;
+        Code lit = {T.lit_lj, T.lit_ent, 0}, dst = {T.dst_lj, T.dst_ent, 0};
+        if (type == 1u) {
+            for (uint32_t i = lane; i < 288u; i += 32u) T.lens[i] = (uint8_t)(i < 144u ? 8 : i < 256u ? 9 : i < 280u ? 7 : 8);
+            __syncwarp();
+            build_code(lit, T.lens, 288, lane);
+            __syncwarp();
+            T.lens[lane] = 5;
+            __syncwarp();
+            build_code(dst, T.lens, 30, lane);
+        } else {
+            int hlit = 0, hdist = 0;
+            if (lane == 0) {
+                hlit = (int)take(b, 5) + 257; hdist = (int)take(b, 5) + 1;
+                const int hclen = (int)take(b, 4) + 4;
                 if (hlit > 286 || hdist > 30) e = 4;
-                uint8_t cl[19];
-                for (int i = 0; i < 19; i++) cl[i] = 0;
-                for (int i = 0; i < hclen && !e; i++) cl[c_order[i]] = (uint8_t)take(b, 3);
-                Huff& hc = T.dist;                                        // borrowed until the real one is built
-                if (!e && build(hc, cl, 19) != 0) e = 4;
+                for (int i = 0; i < 19; i++) T.cl[i] = 0;
+                for (int i = 0; i < hclen && !e; i++) T.cl[c_order[i]] = (uint8_t)take(b, 3);
+            }
+            e = __shfl_sync(FULLM, e, 0); hlit = __shfl_sync(FULLM, hlit, 0); hdist = __shfl_sync(FULLM, hdist, 0);
+            __syncwarp();
+            Code aux = {T.aux_lj, T.aux_ent, 0};
+            if (!e && build_code(aux, T.cl, 19, lane) != 0) e = 4;
+            if (!e && lane == 0) {
                 int idx = 0;
                 while (!e && idx < hlit + hdist) {
-                    const int sym = decode(b, hc);
+                    const int sym = decode_sym(b, aux);
                     if (sym < 0) { e = 5; break; }
                     if (sym < 16) T.lens[idx++] = (uint8_t)sym;
                     else {
@@ -168,15 +202,17 @@ k_verify(const uint8_t* __restrict__ in, uint32_t chunk, uint32_t dict, uint32_t
                     }
                 }
                 if (!e && T.lens[256] == 0) e = 4;
-                if (!e) {
-                    int r = build(T.lit, T.lens, hlit);
-                    if (r < 0 || (r > 0 && hlit - T.lit.count[0] != 1)) e = 4;
-                    r = build(T.dist, T.lens + hlit, hdist);
-                    if (r < 0 || (r > 0 && hdist - T.dist.count[0] != 1)) e = 4;
-                }
+            }
+            e = __shfl_sync(FULLM, e, 0);
+            __syncwarp();
+            if (!e) {
+                // a complete code, or -- the one exception RFC 1951 allows -- a single code of length 1
+                int r = build_code(lit, T.lens, hlit, lane);
+                if (r < 0 || (r > 0 && !(lit.n == 1 && r == (1 << 14)))) e = 4;
+                r = build_code(dst, T.lens + hlit, hdist, lane);
+                if (r < 0 || (r > 0 && !(dst.n <= 1 && (dst.n == 0 || r == (1 << 14))))) e = 4;
             }
         }
-        e = __shfl_sync(FULLM, e, 0);
         if (e) { err = (int)e; break; }
         __syncwarp();
         // symbols
@@ -185,7 +221,7 @@ k_verify(const uint8_t* __restrict__ in, uint32_t chunk, uint32_t dict, uint32_t
             uint32_t what = 0, len = 0, dist = 0, npos = pos;            // what: 0 end of block, 1 match, >= 2 error code
             if (lane == 0) {
                 for (;;) {
-                    const int sym = decode(b, T.lit);
+                    const int sym = decode_sym(b, lit);
                     if (sym < 0) { what = 5; break; }
                     if (sym < 256) {
                         if (npos >= n) { what = 7; break; }
@@ -197,7 +233,7 @@ k_verify(const uint8_t* __restrict__ in, uint32_t chunk, uint32_t dict, uint32_t
                     const int ls = sym - 257;
                     if (ls >= 29) { what = 5; break; }
                     len = c_lbase[ls] + take(b, c_lext[ls]);
-                    const int ds = decode(b, T.dist);
+                    const int ds = decode_sym(b, dst);
                     if (ds < 0 || ds >= 30) { what = 5; break; }
                     dist = c_dbase[ds] + take(b, c_dext[ds]);
                     what = 1;

@@ -275,24 +275,46 @@ static inline void putbits(bitw *w, uint32_t v, int n)
     }
 }
 
-/* RLE of code lengths (scan_tree/send_tree, trees.c:703-793).  Emits (sym, extra, nextra) triples. */
+/* Run-length coding of a code-length sequence with the symbols 16 / 17 / 18 of RFC 1951 3.2.7 (the engine's own policy;
+ * zlib's is scan_tree / send_tree, lib/zlib/trees.c:703-793).  The sequence is cut into MAXIMAL runs of equal lengths and
+ * every run is coded on its own:
+ *   zeros, L of them : as many "18" (138 zeros) as fit; then one "18" (11..137) or "17" (3..10) for the rest, or the
+ *                      last one or two zeros as plain lengths
+ *   v != 0, L of them: v once, then the other L - 1 as "16" (repeat the previous length 6 times) while 3 or more are
+ *                      left -- the last "16" takes 3..6 -- and one or two plain v at the end
+ * Returns the number of (symbol, extra-bits value) pairs.  (GPU: k_huffman rle_lengths, one lane per run.) */
+static int rle_run_count(int v, int L)
+{
+    if (v == 0) { int q = L / 138, r = L % 138; return q + (r >= 3 ? 1 : r); }
+    int R = L - 1, q = R / 6, r = R % 6;
+    return 1 + q + (r >= 3 ? 1 : r);
+}
+static int rle_run_emit(int v, int L, uint8_t *sym, uint8_t *ext)
+{
+    int k = 0;
+    if (v == 0) {
+        while (L >= 138) { sym[k] = 18; ext[k++] = 138 - 11; L -= 138; }
+        if (L >= 11) { sym[k] = 18; ext[k++] = (uint8_t)(L - 11); }
+        else if (L >= 3) { sym[k] = 17; ext[k++] = (uint8_t)(L - 3); }
+        else while (L-- > 0) { sym[k] = 0; ext[k++] = 0; }
+        return k;
+    }
+    sym[k] = (uint8_t)v; ext[k++] = 0;
+    int R = L - 1;
+    while (R >= 6) { sym[k] = 16; ext[k++] = 6 - 3; R -= 6; }
+    if (R >= 3) { sym[k] = 16; ext[k++] = (uint8_t)(R - 3); }
+    else while (R-- > 0) { sym[k] = (uint8_t)v; ext[k++] = 0; }
+    return k;
+}
 static int rle_lengths(const uint8_t *lens, int n, uint8_t *sym, uint8_t *ext)
 {
-    int k = 0, prevlen = -1, curlen, nextlen = lens[0], count = 0, max_count = 7, min_count = 4;
-    if (nextlen == 0) { max_count = 138; min_count = 3; }
-    for (int i = 0; i < n; i++) {
-        curlen = nextlen; nextlen = (i + 1 < n) ? lens[i + 1] : 0xffff;
-        if (++count < max_count && curlen == nextlen) continue;
-        else if (count < min_count) { while (count--) { sym[k] = (uint8_t)curlen; ext[k++] = 0; } }
-        else if (curlen != 0) {
-            if (curlen != prevlen) { sym[k] = (uint8_t)curlen; ext[k++] = 0; count--; }
-            sym[k] = 16; ext[k++] = (uint8_t)(count - 3);
-        } else if (count <= 10) { sym[k] = 17; ext[k++] = (uint8_t)(count - 3); }
-        else { sym[k] = 18; ext[k++] = (uint8_t)(count - 11); }
-        count = 0; prevlen = curlen;
-        if (nextlen == 0) { max_count = 138; min_count = 3; }
-        else if (curlen == nextlen) { max_count = 6; min_count = 3; }
-        else { max_count = 7; min_count = 4; }
+    int k = 0;
+    for (int i = 0; i < n; ) {
+        int j = i + 1;
+        while (j < n && lens[j] == lens[i]) j++;
+        int c = rle_run_emit(lens[i], j - i, sym + k, ext + k);
+        if (c != rle_run_count(lens[i], j - i)) return -1;       /* the two statements of the policy agree */
+        k += c; i = j;
     }
     return k;
 }

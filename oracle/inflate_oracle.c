@@ -1,5 +1,8 @@
 /* inflate_oracle.c -- a plain RFC 1951 decoder.
- * TEST INFRASTRUCTURE ONLY (see oracle.h).  The reference decodes with zlib's inflate through
+ * TEST INFRASTRUCTURE ONLY (see oracle.h).  Its table builder and bit-serial symbol decoder (build / decode below)
+ * follow the structure of Mark Adler's puff (the reference vendors it as lib/zlib/contrib/puff/puff.c:235-258,340-379):
+ * a second, deliberately simple implementation of the format that shares no code with zlib's inflate.c.  The product's
+ * own decoder (k_verify.cu) is a different design (sorted left-justified codes + binary search, built by a warp).  The reference decodes with zlib's inflate through
  * inflateGZIP (src/unzip.c:254-370), which is out of scope for the engine; this decoder exists so
  * the tests can (a) verify round trips without trusting a single implementation and (b) dissect a
  * stream (block types, token counts, where it breaks).  It is checked against the reference's
