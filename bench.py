@@ -433,6 +433,24 @@ def main():
                 size_vs_ref = size_gate(int(rp.out_bytes), cpu)
                 cpu["sample"] = cpu["sample"].replace("the whole", "the first") + f" (of {n * world >> 20} MiB)"
 
+        # ---- the drop-in entry point itself: gzb_zip_fd, tmpfs file -> tmpfs file (read, H2D, kernels, D2H, write), one
+        # process, this GPU; the second call is timed (the first creates the pooled contexts and page-locks the slots) ----
+        e2e_fd = None
+        src_path = os.path.join(tmp, f"in_{corpus}_{n}.bin")
+        if world == 1 and os.path.exists(src_path):
+            dst_path = os.path.join(tmp, "fd_out.gz")
+            times = []
+            for _ in range(3):
+                with open(src_path, "rb") as fi, open(dst_path, "wb") as fo:
+                    t0 = time.perf_counter(); bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=level, n_gpus=1); times.append(time.perf_counter() - t0)
+            with open(dst_path, "rb") as f:
+                f.seek(-8, 2); tr = f.read(8)
+            assert bi == n and bo == res["out_bytes"] + 18 and tr == gz.gzip_trailer(res["crc32"], n), "gzb_zip_fd wrote a different member"
+            os.unlink(dst_path)
+            e2e_fd = {"value": round(n / min(times[1:]) / 1e9, 3), "unit": "GB/s", "cold_first_call": round(n / times[0] / 1e9, 3),
+                      "what": "gzb_zip_fd(n_gpus=1), tmpfs file to tmpfs file, wall clock, best of the 2 calls after the first", "member_bytes": bo}
+            gz.zip_release()
+
         others = []
         if cfg == 1 and world == 1 and not a.no_extra_configs:
             # the other single-GPU configurations of BASELINE.json, short: 3 steps each, same gates
@@ -489,6 +507,8 @@ def main():
                              "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                              "note": "integer/latency-bound path: the HBM fraction is small by construction (SURVEY 8d); see profiles/ for issue-slot utilisation"},
                 "cpu_baseline": cpu, "clocks": res["clocks"]}
+        if e2e_fd:
+            line["e2e_fd"] = e2e_fd
         if member:
             line["config"]["member"] = member
         if others:

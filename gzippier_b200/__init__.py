@@ -32,6 +32,10 @@ class ZipOpts(ctypes.Structure):
                 ("members", ctypes.c_int)]
 
 
+class Shard(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_uint64) for k in ("in_off", "in_bytes", "out_off", "out_bytes")]
+
+
 class GzbError(RuntimeError):
     def __init__(self, code, detail=""):
         self.code = code
@@ -66,6 +70,8 @@ def lib():
         L.gzb_gzip_header.argtypes = [i32, u32, ctypes.c_char_p, vp, ctypes.c_size_t]
         L.gzb_gzip_trailer.argtypes = [u32, u64, vp, ctypes.c_size_t]
         L.gzb_zip_fd.argtypes = [i32, i32, ctypes.POINTER(ZipOpts)]
+        L.gzb_zip_release.restype = None
+        L.gzb_deflate_host_multi.argtypes = [ctypes.POINTER(vp), i32, i32, u32, vp, u64, vp, vp, u64, ctypes.POINTER(Result), ctypes.POINTER(Shard), i32]
         _lib = L
     return _lib
 
@@ -213,3 +219,27 @@ def zip_fd(ifd: int, ofd: int, level: int = 6, rsyncable: bool = False, n_gpus: 
     if rc != OK:
         raise GzbError(rc, lib().gzb_strerror(rc).decode())
     return o.bytes_in, o.bytes_out
+
+
+def zip_release():
+    """Free the contexts and page-locked slots gzb_zip_fd keeps between calls."""
+    lib().gzb_zip_release()
+
+
+def deflate_host_multi(contexts, data, level: int = 6, flags: int = F_FINAL, dict_bytes=None, out=None, compact: bool = True):
+    """gzb_deflate_host_multi: `data` sharded over the given contexts (one per GPU).  -> (raw bytes view, Result, shards)."""
+    import numpy as np
+    a = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+    cap = bound(a.size, flags) + 64 * len(contexts)
+    if out is None:
+        out = np.empty(cap, dtype=np.uint8)
+    d = None
+    if dict_bytes is not None:
+        d = np.frombuffer(dict_bytes, dtype=np.uint8) if not isinstance(dict_bytes, np.ndarray) else dict_bytes
+    hs = (ctypes.c_void_p * len(contexts))(*[c._h for c in contexts])
+    r = Result(); sh = (Shard * len(contexts))()
+    rc = lib().gzb_deflate_host_multi(hs, len(contexts), level, flags, a.ctypes.data if a.size else None, a.size,
+                                      d.ctypes.data if d is not None else None, out.ctypes.data, out.size, ctypes.byref(r), sh, int(compact))
+    if rc != OK:
+        raise GzbError(rc, lib().gzb_last_error(contexts[0]._h).decode())
+    return (out[: r.out_bytes] if compact else out), r, [(s.in_off, s.in_bytes, s.out_off, s.out_bytes) for s in sh]

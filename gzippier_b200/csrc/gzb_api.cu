@@ -9,6 +9,7 @@
 #include <cstring>
 #include <mutex>
 #include <vector>
+#include <thread>
 #include <new>
 
 using namespace gzb;
@@ -620,6 +621,62 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
         return rc;
     }
     total.out_bytes = opos; total.status = GZB_OK;
+    if (result) *result = total;
+    return GZB_OK;
+}
+
+// Host buffers over SEVERAL GPUs in one call: the input is cut into contiguous shards on chunk boundaries (one per
+// context, sizes as even as the grid allows), every shard runs gzb_deflate_host on its own context and host thread with
+// the 32 KiB before it as dictionary, and lands at out + shards[i].out_off (= gzb_bound of the bytes before it, so the
+// shards cannot collide).  No collective: crc32_combine and concatenation are host arithmetic (src/parallel.c:538-546).
+// With compact != 0 the bodies are moved together so that out[0, result->out_bytes) is the fragment run of the whole input.
+int gzb_deflate_host_multi(gzb_ctx** ctxs, int n_ctx, int level, uint32_t flags, const uint8_t* in, uint64_t n, const uint8_t* dict,
+                           uint8_t* out, uint64_t out_cap, gzb_result* result, gzb_shard* shards, int compact)
+{
+    if (!ctxs || n_ctx < 1 || n_ctx > 64 || (n && !in) || !out) return GZB_E_ARG;
+    for (int i = 0; i < n_ctx; i++) if (!ctxs[i]) return GZB_E_ARG;
+    const uint64_t chunk = (flags & GZB_F_RSYNCABLE) ? GZB_RSYNC_CHUNK : GZB_CHUNK;
+    const uint64_t dsz = (flags & GZB_F_RSYNCABLE) ? 0u : GZB_DICT;
+    const uint64_t nchunks = (n + chunk - 1) / chunk;
+    std::vector<gzb_shard> sh((size_t)n_ctx);
+    std::vector<gzb_result> res((size_t)n_ctx);
+    std::vector<int> rcs((size_t)n_ctx, GZB_OK);
+    uint64_t c0 = 0;
+    for (int i = 0; i < n_ctx; i++) {
+        const uint64_t per = nchunks / (uint64_t)n_ctx + ((uint64_t)i < nchunks % (uint64_t)n_ctx ? 1u : 0u);
+        const uint64_t lo = c0 * chunk < n ? c0 * chunk : n, hi = (c0 + per) * chunk < n ? (c0 + per) * chunk : n;
+        sh[(size_t)i].in_off = lo; sh[(size_t)i].in_bytes = hi - lo; sh[(size_t)i].out_off = i ? gzb_bound(lo, flags) : 0; sh[(size_t)i].out_bytes = 0;
+        c0 += per;
+    }
+    if (out_cap < gzb_bound(n, flags) + (uint64_t)n_ctx * 64u) return fail(ctxs[0], GZB_E_OUT_FULL, "out_cap < gzb_bound(n) + 64 per shard");
+    int last = 0;                                             // the last shard that holds bytes ends the stream
+    for (int i = 0; i < n_ctx; i++) if (sh[(size_t)i].in_bytes || i == 0) last = i;
+    auto work = [&](int i) {
+        const gzb_shard& q = sh[(size_t)i];
+        if (q.in_bytes == 0 && i != last) { memset(&res[(size_t)i], 0, sizeof(gzb_result)); return; }
+        const uint8_t* d = q.in_off == 0 ? dict : (dsz ? in + q.in_off - dsz : nullptr);
+        const uint32_t f = (flags & ~GZB_F_FINAL) | ((i == last && (flags & GZB_F_FINAL)) ? GZB_F_FINAL : 0u);
+        rcs[(size_t)i] = gzb_deflate_host(ctxs[i], level, f, in + q.in_off, q.in_bytes, d, out + q.out_off, gzb_bound(q.in_bytes, flags), &res[(size_t)i]);
+    };
+    std::vector<std::thread> th;
+    for (int i = 1; i < n_ctx; i++) th.emplace_back(work, i);
+    work(0);
+    for (auto& t : th) t.join();
+    for (int i = 0; i < n_ctx; i++) if (rcs[(size_t)i] != GZB_OK) {
+        if (i) snprintf(ctxs[0]->err, sizeof(ctxs[0]->err), "shard %d: %.480s", i, ctxs[i]->err);
+        return rcs[(size_t)i];
+    }
+    gzb_result total; memset(&total, 0, sizeof(total));
+    uint64_t opos = 0;
+    for (int i = 0; i < n_ctx; i++) {
+        const gzb_result& r = res[(size_t)i];
+        sh[(size_t)i].out_bytes = r.out_bytes;
+        if (compact) { if (sh[(size_t)i].out_off != opos && r.out_bytes) memmove(out + opos, out + sh[(size_t)i].out_off, r.out_bytes); sh[(size_t)i].out_off = opos; }
+        opos += r.out_bytes;
+        total.crc32 = gzb_crc32_combine(total.crc32, r.crc32, sh[(size_t)i].in_bytes);
+        total.in_bytes += r.in_bytes; total.out_bytes += r.out_bytes; total.n_chunks += r.n_chunks; total.n_blocks += r.n_blocks;
+    }
+    if (shards) for (int i = 0; i < n_ctx; i++) shards[i] = sh[(size_t)i];
     if (result) *result = total;
     return GZB_OK;
 }

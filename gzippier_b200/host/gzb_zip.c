@@ -8,7 +8,7 @@
  *   reader   (caller's thread)  reads ifd in batches of BATCH bytes into pinned slots, keeps the
  *                               32 KiB that precede a batch right in front of it (:767-774), and
  *                               looks one batch ahead to know which one is final (:764)
- *   workers  (2 per GPU)        each owns a context (its own streams): batch i goes to worker
+ *   workers  (2 per GPU)        each uses a context of the process-wide pool (its own streams): batch i goes to worker
  *                               i mod W, which calls gzb_deflate_host on it.  Two workers per GPU
  *                               put the copies of one batch under the kernels of the other.
  *   writer   (one thread)       header, fragments in batch order, CRCs folded with
@@ -65,9 +65,11 @@ static int writen(int fd, const uint8_t *buf, size_t len)
     return 0;
 }
 
-/* A regular file is read by READERS threads with pread (one read() stream from the page cache is ~5 GB/s, a third
- * of what one GPU takes); anything else -- a pipe, a tty -- sequentially, like the reference's readn (:66-84). */
-#define READERS 4
+/* A regular file is read by g_readers threads with pread (one read() stream from the page cache is ~5 GB/s, a quarter
+ * of what one GPU takes): 8 per GPU, at most 32 and at most the CPUs that are online; anything else -- a pipe, a tty --
+ * sequentially, like the reference's readn (:66-84).  A regular output file is written the same way (pwrite). */
+#define READERS 32
+static int g_readers = 8;
 typedef struct { int fd; uint8_t *buf; size_t len; off_t off; ssize_t got; } pread_job;
 static void *pread_worker(void *arg)
 {
@@ -86,8 +88,9 @@ static ssize_t read_batch(int fd, uint8_t *buf, size_t len, int regular, off_t *
 {
     if (!regular) return readn(fd, buf, len);
     pread_job j[READERS]; pthread_t th[READERS]; int started[READERS];
-    const size_t part = ((len / READERS) + 4095u) & ~(size_t)4095u;
-    for (int k = 0; k < READERS; k++) {
+    const int nr = g_readers;
+    const size_t part = ((len / (size_t)nr) + 4095u) & ~(size_t)4095u;
+    for (int k = 0; k < nr; k++) {
         const size_t lo = (size_t)k * part < len ? (size_t)k * part : len;
         const size_t hi = lo + part < len ? lo + part : len;
         j[k].fd = fd; j[k].buf = buf + lo; j[k].len = hi - lo; j[k].off = *pos + (off_t)lo; j[k].got = 0;
@@ -96,7 +99,7 @@ static ssize_t read_batch(int fd, uint8_t *buf, size_t len, int regular, off_t *
     }
     pread_worker(&j[0]);
     ssize_t total = 0; int shorted = 0;
-    for (int k = 0; k < READERS; k++) {
+    for (int k = 0; k < nr; k++) {
         if (started[k]) pthread_join(th[k], NULL);
         if (j[k].got < 0) return -1;
         if (!shorted) total += j[k].got;            /* bytes after a short part belong to a file that grew: ignore */
@@ -104,6 +107,40 @@ static ssize_t read_batch(int fd, uint8_t *buf, size_t len, int regular, off_t *
     }
     *pos += (off_t)total;
     return total;
+}
+
+typedef struct { int fd; const uint8_t *buf; size_t len; off_t off; int rc; } pwrite_job;
+static void *pwrite_worker(void *arg)
+{
+    pwrite_job *j = (pwrite_job *)arg;
+    size_t done = 0;
+    while (done < j->len) {
+        ssize_t r = pwrite(j->fd, j->buf + done, j->len - done, j->off + (off_t)done);
+        if (r < 0) { if (errno == EINTR) continue; j->rc = -1; return NULL; }
+        done += (size_t)r;
+    }
+    j->rc = 0;
+    return NULL;
+}
+/* len bytes at *pos of a regular file, in parts of at least 4 MiB on up to g_readers threads; *pos advances */
+static int write_batch(int fd, const uint8_t *buf, size_t len, int regular, off_t *pos)
+{
+    if (!regular) return writen(fd, buf, len);
+    int np = (int)(len >> 22); if (np > g_readers) np = g_readers; if (np < 1) np = 1;
+    pwrite_job j[READERS]; pthread_t th[READERS]; int started[READERS];
+    const size_t part = ((len / (size_t)np) + 4095u) & ~(size_t)4095u;
+    for (int k = 0; k < np; k++) {
+        const size_t lo = (size_t)k * part < len ? (size_t)k * part : len;
+        const size_t hi = (k == np - 1) ? len : (lo + part < len ? lo + part : len);
+        j[k].fd = fd; j[k].buf = buf + lo; j[k].len = hi - lo; j[k].off = *pos + (off_t)lo; j[k].rc = 0;
+        started[k] = k > 0 && j[k].len && pthread_create(&th[k], NULL, pwrite_worker, &j[k]) == 0;
+        if (k > 0 && !started[k]) pwrite_worker(&j[k]);
+    }
+    pwrite_worker(&j[0]);
+    int rc = 0;
+    for (int k = 0; k < np; k++) { if (started[k]) pthread_join(th[k], NULL); if (j[k].rc) rc = -1; }
+    *pos += (off_t)len;
+    return rc;
 }
 
 enum { S_FREE = 0, S_READ, S_DONE };
@@ -124,6 +161,7 @@ typedef struct pipe_s {
     int rc;                 /* first error; everybody stops */
     int level; uint32_t flags; uint64_t batch, dict_sz, out_cap;
     int ofd; gzb_zip_opts *o; uint32_t crc;
+    int out_regular; off_t opos;       /* regular output file: written with pwrite at opos (several threads per batch) */
     gzb_ctx *ctx[MAX_WORKERS];
 } pipe_t;
 
@@ -176,14 +214,14 @@ static void *writer(void *arg)
         if (p->o->members && i > 0) {             /* a member per batch: its own header (no name) ... */
             uint8_t h[16];
             const int hn = gzb_gzip_header(p->level, p->o->mtime, NULL, h, sizeof(h));
-            if (hn < 0 || writen(p->ofd, h, (size_t)hn)) { fail(p, GZB_E_IO); return NULL; }
+            if (hn < 0 || write_batch(p->ofd, h, (size_t)hn, p->out_regular, &p->opos)) { fail(p, GZB_E_IO); return NULL; }
             p->o->bytes_out += (uint64_t)hn;
         }
-        if (writen(p->ofd, s->out, s->res.out_bytes)) { fail(p, GZB_E_IO); return NULL; }
+        if (write_batch(p->ofd, s->out, s->res.out_bytes, p->out_regular, &p->opos)) { fail(p, GZB_E_IO); return NULL; }
         if (p->o->members) {                      /* ... and its own trailer */
             uint8_t tr[8];
             gzb_gzip_trailer(s->res.crc32, s->n, tr, sizeof(tr));
-            if (writen(p->ofd, tr, 8)) { fail(p, GZB_E_IO); return NULL; }
+            if (write_batch(p->ofd, tr, 8, p->out_regular, &p->opos)) { fail(p, GZB_E_IO); return NULL; }
             p->o->bytes_out += 8;
         }
         p->crc = gzb_crc32_combine(p->crc, s->res.crc32, s->n);
@@ -199,16 +237,56 @@ static void *writer(void *arg)
 
 static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec; }
 
-/* Inputs that end within SMALL bytes -- most files a gzip ever sees -- take one call on pageable memory: no pinned
- * slots (page-locking costs ~0.3 s per GiB), no threads. */
-#define SMALL ((size_t)32 << 20)
-static int zip_small(int ofd, gzb_zip_opts *o, uint32_t flags, const uint8_t *data, uint64_t n)
+/* ---- what outlives a call ---------------------------------------------------------------------------------------
+ * Creating a context (CUDA streams, 2 GiB of device scratch) and page-locking the batch slots (~0.3 s per GiB) cost more
+ * than compressing a few GiB does, so both are kept for the next call of the process: the reference's buffer pools live
+ * for a whole parallel_zip() (src/parallel.c:327-347), these live until gzb_zip_release().  Calls are serialised. */
+static struct {
+    pthread_mutex_t mu;
+    gzb_ctx *ctx[MAX_WORKERS]; int nctx, ng;
+    uint8_t *in[MAX_SLOTS], *out[MAX_SLOTS]; uint64_t batch, out_cap;
+} g_pool = { PTHREAD_MUTEX_INITIALIZER, {0}, 0, 0, {0}, {0}, 0, 0 };
+
+static void pool_free_slots(void)
 {
-    gzb_ctx *ctx = NULL;
+    for (int i = 0; i < MAX_SLOTS; i++) {
+        if (g_pool.in[i]) gzb_host_free(g_pool.in[i]);
+        if (g_pool.out[i]) gzb_host_free(g_pool.out[i]);
+        g_pool.in[i] = g_pool.out[i] = NULL;
+    }
+    g_pool.batch = g_pool.out_cap = 0;
+}
+void gzb_zip_release(void)
+{
+    pthread_mutex_lock(&g_pool.mu);
+    pool_free_slots();
+    for (int w = 0; w < g_pool.nctx; w++) { gzb_destroy(g_pool.ctx[w]); g_pool.ctx[w] = NULL; }
+    g_pool.nctx = g_pool.ng = 0;
+    pthread_mutex_unlock(&g_pool.mu);
+}
+/* contexts for 2 workers on each of ng GPUs (worker w on GPU w % ng); the pool's lock is held */
+static int pool_contexts(int ng)
+{
+    if (g_pool.ng != ng) {
+        for (int w = 0; w < g_pool.nctx; w++) { gzb_destroy(g_pool.ctx[w]); g_pool.ctx[w] = NULL; }
+        g_pool.nctx = 0; g_pool.ng = ng;
+    }
+    while (g_pool.nctx < 2 * ng) {
+        int rc = gzb_create(g_pool.nctx % ng, &g_pool.ctx[g_pool.nctx]);
+        if (rc != GZB_OK) return rc;
+        g_pool.nctx++;
+    }
+    return GZB_OK;
+}
+
+/* Inputs that end within SMALL bytes -- most files a gzip ever sees -- take one call on pageable memory: no pinned
+ * slots, no threads. */
+#define SMALL ((size_t)32 << 20)
+static int zip_small(gzb_ctx *ctx, int ofd, gzb_zip_opts *o, uint32_t flags, const uint8_t *data, uint64_t n)
+{
     uint8_t *out = NULL, tr[8];
     gzb_result r;
-    int rc = gzb_create(0, &ctx);
-    if (rc != GZB_OK) return rc;
+    int rc = GZB_OK;
     const uint64_t cap = gzb_bound(n, flags);
     if (!(out = (uint8_t *)malloc(cap))) rc = GZB_E_NOMEM;
     if (rc == GZB_OK) rc = gzb_deflate_host(ctx, o->level, flags | GZB_F_FINAL, data, n, NULL, out, cap, &r);
@@ -218,7 +296,7 @@ static int zip_small(int ofd, gzb_zip_opts *o, uint32_t flags, const uint8_t *da
         if (writen(ofd, tr, 8)) rc = GZB_E_IO;
         o->bytes_in = n; o->bytes_out += r.out_bytes + 8;
     }
-    free(out); gzb_destroy(ctx);
+    free(out);
     return rc;
 }
 
@@ -238,6 +316,15 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     struct stat st;
     off_t pos = 0;
     const int regular = fstat(ifd, &st) == 0 && S_ISREG(st.st_mode) && (pos = lseek(ifd, 0, SEEK_CUR)) >= 0;
+    /* a regular output file that is not in append mode is written with pwrite at explicit offsets */
+    const int oflags = fcntl(ofd, F_GETFL);
+    p->out_regular = fstat(ofd, &st) == 0 && S_ISREG(st.st_mode) && oflags >= 0 && !(oflags & O_APPEND) && (p->opos = lseek(ofd, 0, SEEK_CUR)) >= 0;
+    {
+        long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+        int nr = 8 * ng; if (nr > READERS) nr = READERS; if (ncpu > 0 && nr > (int)ncpu) nr = (int)ncpu; if (nr < 1) nr = 1;
+        g_readers = nr;
+    }
+    pthread_mutex_lock(&g_pool.mu);                  /* one call at a time: contexts and pinned slots are the pool's */
 #ifdef F_SETPIPE_SZ
     if (!regular) { (void)fcntl(ifd, F_SETPIPE_SZ, 1 << 20); (void)fcntl(ofd, F_SETPIPE_SZ, 1 << 20); }   /* pipes: fewer, larger transfers */
 #endif
@@ -254,7 +341,7 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
 
     int hn = gzb_gzip_header(o->level, o->mtime, o->name, hdr, sizeof(hdr));
     if (hn < 0) { rc = hn; goto done; }
-    if (writen(ofd, hdr, (size_t)hn)) { rc = GZB_E_IO; goto done; }
+    if (write_batch(ofd, hdr, (size_t)hn, p->out_regular, &p->opos)) { rc = GZB_E_IO; goto done; }
     o->bytes_in = 0; o->bytes_out = (uint64_t)hn;
 
     /* look at the first SMALL bytes: is that all there is? */
@@ -262,9 +349,16 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     if (!(peek = (uint8_t *)malloc(peek_len))) { rc = GZB_E_NOMEM; goto done; }
     ssize_t pk = read_batch(ifd, peek, peek_len, regular, &pos);
     if (pk < 0) { rc = GZB_E_IO; goto done; }
-    if ((size_t)pk < peek_len) { rc = zip_small(ofd, o, p->flags, peek, (uint64_t)pk); goto done; }
-
-    for (int w = 0; w < p->nworkers; w++) if ((rc = gzb_create(w % ng, &p->ctx[w])) != GZB_OK) goto done;
+    if ((rc = pool_contexts(ng)) != GZB_OK) goto done;
+    for (int w = 0; w < p->nworkers; w++) p->ctx[w] = g_pool.ctx[w];
+    if ((size_t)pk < peek_len) {
+        if (p->out_regular) lseek(ofd, p->opos, SEEK_SET);          /* the small path writes sequentially */
+        rc = zip_small(p->ctx[0], ofd, o, p->flags, peek, (uint64_t)pk);
+        if (p->out_regular) p->opos = lseek(ofd, 0, SEEK_CUR);
+        goto done;
+    }
+    if (g_pool.batch != p->batch || g_pool.out_cap != p->out_cap) { pool_free_slots(); g_pool.batch = p->batch; g_pool.out_cap = p->out_cap; }
+    for (int i = 0; i < p->nslots; i++) { p->s[i].in = g_pool.in[i]; p->s[i].out = g_pool.out[i]; }
     for (int w = 0; w < p->nworkers; w++) {
         wa[w].p = p; wa[w].w = w;
         if (pthread_create(&th[w], NULL, worker, &wa[w])) { fail(p, GZB_E_NOMEM); break; }
@@ -277,8 +371,10 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     for (uint64_t i = 0;; i++) {
         slot *s = &p->s[i % (uint64_t)p->nslots];
         if (!s->in) {                             /* slots are page-locked on first use, under the work of the earlier batches */
+            const int si = (int)(i % (uint64_t)p->nslots);
             int arc = gzb_host_alloc(p->ctx[0], GZB_DICT + p->batch, (void **)&s->in);
-            if (arc == GZB_OK) arc = gzb_host_alloc(p->ctx[0], p->out_cap, (void **)&s->out);
+            g_pool.in[si] = s->in;
+            if (arc == GZB_OK) { arc = gzb_host_alloc(p->ctx[0], p->out_cap, (void **)&s->out); g_pool.out[si] = s->out; }
             if (arc != GZB_OK) { fail(p, arc); break; }
         }
         pthread_mutex_lock(&p->mu);
@@ -320,15 +416,15 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     if (rc == GZB_OK && !o->members) {
         uint8_t tr[8];
         gzb_gzip_trailer(p->crc, o->bytes_in, tr, sizeof(tr));
-        if (writen(ofd, tr, 8)) rc = GZB_E_IO; else o->bytes_out += 8;
+        if (write_batch(ofd, tr, 8, p->out_regular, &p->opos)) rc = GZB_E_IO; else o->bytes_out += 8;
     }
     t_stream = now_s();
 done:
     free(peek);
-    for (int i = 0; i < p->nslots; i++) { if (p->s[i].in) gzb_host_free(p->s[i].in); if (p->s[i].out) gzb_host_free(p->s[i].out); }
-    for (int w = 0; w < p->nworkers; w++) if (p->ctx[w]) gzb_destroy(p->ctx[w]);
+    pthread_mutex_unlock(&g_pool.mu);                /* contexts and slots stay in the pool (gzb_zip_release) */
     pthread_mutex_destroy(&p->mu); pthread_cond_destroy(&p->cv);
-    if (regular) lseek(ifd, pos, SEEK_SET);          /* leave the descriptor where a sequential reader would */
+    if (regular) lseek(ifd, pos, SEEK_SET);          /* leave the descriptors where sequential I/O would */
+    if (p->out_regular) lseek(ofd, p->opos, SEEK_SET);
     if (verbose)
         fprintf(stderr, "gzb_zip_fd: rc %d, %llu -> %llu bytes; contexts + threads %.3f s, read/compress/write %.3f s (%.2f GB/s), teardown %.3f s\n",
                 rc, (unsigned long long)o->bytes_in, (unsigned long long)o->bytes_out, t_setup - t0, t_stream - t_setup,

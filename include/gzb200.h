@@ -126,6 +126,17 @@ int gzb_deflate_host(gzb_ctx *ctx, int level, uint32_t flags,
                      const uint8_t *in, uint64_t n, const uint8_t *dict,
                      uint8_t *out, uint64_t out_cap, gzb_result *result);
 
+/* The same over SEVERAL GPUs in one call (one context per GPU, created by the caller): contiguous shards on chunk
+ * boundaries, the 32 KiB before a shard as its dictionary, no collective -- what parallel_zip does with -j N compress
+ * threads (src/parallel.c:699-834), with a GPU where a thread stood.  Shard i's body lands at out + shards[i].out_off
+ * (out_cap >= gzb_bound(n) + 64 * n_ctx); compact != 0 moves the bodies together so that out[0, result->out_bytes) is the
+ * fragment run of the whole input.  crc32 in *result is folded with gzb_crc32_combine.  shards may be NULL. */
+typedef struct gzb_shard { uint64_t in_off, in_bytes, out_off, out_bytes; } gzb_shard;
+int gzb_deflate_host_multi(gzb_ctx **ctx, int n_ctx, int level, uint32_t flags,
+                           const uint8_t *in, uint64_t n, const uint8_t *dict,
+                           uint8_t *out, uint64_t out_cap, gzb_result *result,
+                           gzb_shard *shards, int compact);
+
 /* CRC-32 on the device (replaces crc32z -> zlib crc32, src/parallel.c:476-486,
  * lib/zlib/crc32.c:202-297).  crc is the running value, 0 to start. */
 int gzb_crc32_device(gzb_ctx *ctx, uint32_t crc, const uint8_t *d_in, uint64_t n,
@@ -162,6 +173,10 @@ typedef struct gzb_zip_opts {
                              * (src/unzip.c:361, src/gzip.c:1024-1030) -- hence off by default. */
 } gzb_zip_opts;
 int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *opts);
+/* gzb_zip_fd keeps its contexts and page-locked batch slots for the next call of the process (creating them costs more
+ * than compressing a few GiB); this frees them.  Stands where the reference frees its pools at the end of parallel_zip
+ * (src/parallel.c:820-833). */
+void gzb_zip_release(void);
 
 /* Page-locked host memory for the buffers handed to gzb_deflate_host (which then DMAs straight from / to them
  * instead of staging).  Stands where the reference's buffer pools stood (src/parallel.c:169-259: get_space /

@@ -167,6 +167,31 @@ def test_incompressible_chunks_are_stored_without_a_search(gz, orc, ctx, monkeyp
         c.close()
 
 
+def test_host_call_over_several_contexts(gz, orc):
+    """gzb_deflate_host_multi: contiguous shards on chunk boundaries, one context (GPU) each, 32 KiB halo, host
+    crc32_combine; compacted, the bodies are exactly the one-call body.  (One GPU is enough: contexts may share a device.)"""
+    import torch
+    ndev = torch.cuda.device_count()
+    for nctx in (1, 2, 3, 5):
+        cs = [gz.Context(i % ndev) for i in range(nctx)]
+        try:
+            for n in (0, 1, gz.CHUNK, 2 * gz.CHUNK + 1, 11 * gz.CHUNK + 4321):
+                d = gz.corpus("mixed", n, seed=51)
+                want = orc.engine_model(d, 6).tobytes() if n else None
+                raw, r, sh = gz.deflate_host_multi(cs, d, 6)
+                assert r.in_bytes == n and r.crc32 == zlib.crc32(d.tobytes())
+                if n:
+                    assert raw.tobytes() == want
+                else:
+                    assert zlib.decompress(raw.tobytes(), -15) == b""
+                assert sum(x[1] for x in sh) == n and all(x[0] % gz.CHUNK == 0 for x in sh)
+                # not compacted: every body where the shard table says
+                out, r2, sh2 = gz.deflate_host_multi(cs, d, 6, compact=False)
+                assert b"".join(out[o: o + l].tobytes() for _, _, o, l in sh2) == raw.tobytes()
+        finally:
+            for c in cs: c.close()
+
+
 def test_host_call_with_a_smaller_output_buffer(gz, orc, ctx):
     """gzb_deflate_host accepts out_cap < gzb_bound(n) (a caller that knows its ratio need not page-lock n bytes of output)
     and reports GZB_E_OUT_FULL instead of writing past it; the context stays usable."""
@@ -319,6 +344,16 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
         m = dst.read_bytes()
         assert bi == n and bo == len(m)
         assert m[:10] == gz.gzip_header(6) and m[10:-8] == want and m[-8:] == gz.gzip_trailer(zlib.crc32(d.tobytes()), n)
+    # the contexts and pinned slots of the last call are still in the pool: the same call again, then an explicit release
+    with open(src, "rb") as fi, open(dst, "wb") as fo:
+        bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
+    assert dst.read_bytes() == m
+    gz.zip_release()
+    with open(src, "rb") as fi, open(dst, "r+b") as fo:         # an output file that already holds bytes: written from the current offset
+        fo.seek(7)
+        bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
+        assert fo.tell() == 7 + len(m)
+    assert dst.read_bytes()[7:] == m
     # a pipe on both sides
     monkeypatch.setenv("GZB_ZIP_BATCH_MB", "2")
     r_in, w_in = os.pipe(); r_out, w_out = os.pipe()
