@@ -184,7 +184,7 @@ def test_host_call_over_several_contexts(gz, orc):
                     assert raw.tobytes() == want
                 else:
                     assert zlib.decompress(raw.tobytes(), -15) == b""
-                assert sum(x[1] for x in sh) == n and all(x[0] % gz.CHUNK == 0 for x in sh)
+                assert sum(x[1] for x in sh) == n and all(x[0] % gz.CHUNK == 0 for x in sh if x[1])
                 # not compacted: every body where the shard table says
                 out, r2, sh2 = gz.deflate_host_multi(cs, d, 6, compact=False)
                 assert b"".join(out[o: o + l].tobytes() for _, _, o, l in sh2) == raw.tobytes()
