@@ -23,7 +23,7 @@ constexpr int      MAXD        = 32768;           // farthest match (deflate's l
 constexpr int      TOO_FAR     = 4096;            // lib/zlib/deflate.c:110-112
 constexpr int      HBITS       = 14;              // buckets of the 6-byte chain table
 constexpr int      H4BITS      = 12;              // buckets of the 4-byte single-entry table
-constexpr int      H3BITS      = 12;              // buckets of the 3-byte single-entry table
+constexpr int      H3BITS      = 11;              // buckets of the 3-byte single-entry table
 constexpr int      BLOCK_SPAN  = 65536;           // input bytes per deflate block
 constexpr int      MAX_BPC     = MAX_CHUNK / BLOCK_SPAN;   // blocks per chunk
 constexpr int      LZ_THREADS  = 1024;

@@ -31,7 +31,7 @@
 //   link   72 KiB  u16 delta to the previous position in the same 6-byte bucket (0xFFFF = none),
 //                  indexed by stream position mod LINK_RING; deltas need no sliding
 //   head   32 KiB  u16 last position (mod 64 Ki) per 6-byte bucket -- inserter-private
-//   head3/4 8+8 KiB u16 last position per 3-byte / 4-byte bucket (single entry, no chain)
+//   head3/4 8+16 KiB u32 last position + 1 per 3-byte / 4-byte bucket (single entry, no chain; kept with atomicMax)
 //   c3/c4  8+8 KiB per-position delta to the most recent 3-byte / 4-byte twin, double-buffered per tile
 //   mlen/mdist 12 KiB  per-position best match of the last two tiles
 //   jump    4 KiB  parse scratch (window exit functions)
@@ -41,7 +41,7 @@
 namespace gzb {
 
 // cycle counters (debugging aid, tools/lzprof.py; compiled in with -DGZB_LZPROF only), summed over CTAs:
-// 0 search (warp 0), 1-3 its waits (counter slot, tile inserted, tile parsed), 7 tiles, 8-10 time in insert_tile of the
+// 0 search (warp 28), 1-3 its waits (counter slot, tile inserted, tile parsed), 7 tiles, 8-10 time in insert_tile of the
 // 6-byte / 3-byte / 4-byte table warp, 11 time in parse_emit_tile (thread 0 of the parser group), 12-15 its phases
 __device__ unsigned long long g_lzprof[16];
 #ifdef GZB_LZPROF
@@ -64,8 +64,8 @@ struct Smem {
     uint32_t ring32[RING / 4 + RING_MIRROR / 4];   // + mirror of the first bytes: compare loops never wrap
     uint16_t link[LINK_RING];
     uint16_t head[1 << HBITS];
-    uint16_t head3[1 << H3BITS];
-    uint16_t head4[1 << H4BITS];
+    uint32_t head3[1 << H3BITS];          // stream position + 1 of the bucket's most recent string, 0 = none yet
+    uint32_t head4[1 << H4BITS];
     uint16_t c3[2][TILE];
     uint16_t c4[2][TILE];
     uint16_t mdist[MRING];                // dist-1, 0xFFFF = no match
@@ -261,10 +261,11 @@ __device__ __forceinline__ uint32_t sweep_pair(uint32_t w, uint32_t p16)
 template <int KIND>
 __device__ __forceinline__ void sweep_slice(Smem& S, uint32_t t, uint32_t lane)
 {
-    constexpr uint32_t WORDS = (KIND == 0 ? (1u << HBITS) : KIND == 1 ? (1u << H3BITS) : (1u << H4BITS)) / 2u / 8u;   // words per slice
+    static_assert(KIND == 0, "only the 16-bit chain table ages");
+    constexpr uint32_t WORDS = (1u << HBITS) / 2u / 8u;   // words per slice
     static_assert(WORDS % 128u == 0, "sweep_slice: four words per lane and trip");
     const uint32_t p16 = (t * TILE) & 0xFFFFu;
-    uint4* tab = reinterpret_cast<uint4*>(KIND == 0 ? S.head : KIND == 1 ? S.head3 : S.head4) + (t & 7u) * (WORDS / 4u);
+    uint4* tab = reinterpret_cast<uint4*>(S.head) + (t & 7u) * (WORDS / 4u);
     for (uint32_t i = lane; i < WORDS / 4u; i += 32u) {
         uint4 v = tab[i];
         v.x = sweep_pair(v.x, p16); v.y = sweep_pair(v.y, p16); v.z = sweep_pair(v.z, p16); v.w = sweep_pair(v.w, p16);
@@ -280,7 +281,8 @@ __device__ void insert_tile(Smem& S, uint32_t sbase, uint32_t t, uint32_t n_s, u
     const uint32_t base = t * TILE;                                           // < n_s
     const uint32_t nsteps = min((uint32_t)GROUPS_PER_TILE, (n_s - base + 31u) / 32u);   // nothing past the end is ever searched
     const uint32_t ring_s = sbase + (uint32_t)offsetof(Smem, ring32);
-    const uint32_t table_s = sbase + (uint32_t)(KIND == 0 ? offsetof(Smem, head) : KIND == 1 ? offsetof(Smem, head3) : offsetof(Smem, head4));
+    static_assert(KIND == 0, "the exchange step serves the 6-byte chain table; the single-entry tables use insert_tile_max");
+    const uint32_t table_s = sbase + (uint32_t)offsetof(Smem, head);
     // where the deltas go; a tile's link slots are contiguous (LINK_RING % TILE == 0)
     static_assert(LINK_RING % TILE == 0, "a tile's link slots must not wrap");
     uint32_t dst = sbase + (KIND == 0 ? (uint32_t)offsetof(Smem, link) + 2u * (base % LINK_RING + lane)
@@ -324,6 +326,48 @@ __device__ void insert_tile(Smem& S, uint32_t sbase, uint32_t t, uint32_t n_s, u
         ta = tn;
         __syncwarp();
     }
+}
+
+// The single-entry tables (KIND 1 / 2: most recent 3-byte / 4-byte twin) need no chain, so they need no exchange either:
+// an entry is the stream position + 1 of the bucket's most recent string, and a step is ONE shared-memory atomicMax per
+// lane.  Whatever order the hardware serves the lanes in, the table ends the step holding the highest position of every
+// bucket, and consecutive steps do not depend on one another through registers, so they pipeline (the exchange of
+// insert_tile costs two dependent shared-memory round trips per step, and 57 % / 37 % of the steps of text have lanes that
+// share a 3-byte / 4-byte bucket and pay two more).  The value a lane gets back is the table's value before ITS update.
+// When the lanes that share a bucket are served in ascending lane order -- what the hardware does, as far as measured --
+// that value is exactly what the lane wants: the position of the nearest lower lane of its bucket, or for the lowest one
+// the bucket's string from before the step.  Any other order hands some lane a position ABOVE its own (a higher lane of
+// its bucket went first), which is what the step checks; only then MATCH.ANY groups the lanes (~400 cycles), a lane's
+// twin is the nearest lower lane of its group, and the lowest lane takes the one value of its group that is not a
+// position of this step (held by whichever lane was served first).
+template <int KIND>
+__device__ void insert_tile_max(Smem& S, uint32_t sbase, uint32_t t, uint32_t n_s, uint32_t lane)
+{
+    static_assert(KIND == 1 || KIND == 2, "single-entry tables only");
+    const uint32_t base = t * TILE;
+    const uint32_t nsteps = min((uint32_t)GROUPS_PER_TILE, (n_s - base + 31u) / 32u);
+    const uint32_t ring_s = sbase + (uint32_t)offsetof(Smem, ring32);
+    uint32_t* table = KIND == 1 ? S.head3 : S.head4;
+    uint16_t* dst = (KIND == 1 ? S.c3[t & 1u] : S.c4[t & 1u]) + lane;
+    constexpr uint32_t REACH = KIND == 1 ? (uint32_t)TOO_FAR : 32767u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll 2
+    for (uint32_t i = 0; i < nsteps; i++) {
+        const uint32_t p1 = base + i * 32u + lane + 1u;                          // this lane's position + 1
+        const uint32_t b = bucket_at<KIND>(ring_s, p1 - 1u);
+        uint32_t prev = atomicMax(&table[b], p1);
+        if (__any_sync(FULL, prev >= p1)) {                                      // served out of order (see above)
+            const uint32_t same = __match_any_sync(FULL, b);
+            // exactly one lane of every group -- the one served first -- holds the bucket's value from before the step
+            const uint32_t holders = __ballot_sync(FULL, prev <= base + i * 32u);
+            const uint32_t first = __shfl_sync(FULL, prev, __ffs(same & holders) - 1);
+            const uint32_t lower = same & lt_mask;
+            prev = lower ? base + i * 32u + (uint32_t)(31 - __clz(lower)) + 1u : first;
+        }
+        const uint32_t d = p1 - prev;                                            // prev == 0 (none yet): d = p1 > REACH only if p1 > REACH ...
+        dst[i * 32u] = (uint16_t)((prev != 0u && d <= REACH) ? d : 0u);          // ... so test prev explicitly
+    }
+    __syncwarp();
 }
 
 // Best match for the 32 positions of one group (one warp).  Semantics: engine_model.c gzm_find_matches.
@@ -687,8 +731,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
         }
         // ---- per-run reset ----
         for (uint32_t i = tid; i < (1u << HBITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head)[i] = TABLE_FILL;
-        for (uint32_t i = tid; i < (1u << H3BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head3)[i] = TABLE_FILL;
-        for (uint32_t i = tid; i < (1u << H4BITS) / 2; i += LZ_THREADS) reinterpret_cast<uint32_t*>(S.head4)[i] = TABLE_FILL;
+        for (uint32_t i = tid; i < (1u << H3BITS); i += LZ_THREADS) S.head3[i] = 0;
+        for (uint32_t i = tid; i < (1u << H4BITS); i += LZ_THREADS) S.head4[i] = 0;
         for (uint32_t i = tid; i < 288u; i += LZ_THREADS) S.lfreq[i] = 0;
         if (tid < 32u) S.dfreq[tid] = 0;
         __syncthreads();
@@ -715,8 +759,8 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 if (t >= 2u) mbar_wait(GZB_BAR(sbase, bar_srch, t - 2u), par_of(t - 2u));   // its link / twin slots are written now
                 LZPROF(const long long i0 = clock64();)
                 if (role == ROLE_INS0) insert_tile<0>(S, sbase, t, n_s, lane);
-                else if (role == ROLE_INS1) insert_tile<1>(S, sbase, t, n_s, lane);
-                else insert_tile<2>(S, sbase, t, n_s, lane);
+                else if (role == ROLE_INS1) insert_tile_max<1>(S, sbase, t, n_s, lane);
+                else insert_tile_max<2>(S, sbase, t, n_s, lane);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(GZB_BAR(sbase, bar_ins, t));
                 LZPROF(if (lane == 0) atomicAdd(&g_lzprof[8 + role], (unsigned long long)(clock64() - i0));)
@@ -738,7 +782,7 @@ k_lz77(const uint8_t* __restrict__ in, uint64_t n_bytes, uint32_t halo, uint32_t
                 } else if (gtid == 0) mbar_arrive(GZB_BAR(sbase, bar_parse, t));
             }
         } else {
-            for (uint32_t t = 0; t < ntiles; t++) search_tile(S, sbase, lp, t, first_ctile, D, chunk, n_s, np, lane, warp == 0u);
+            for (uint32_t t = 0; t < ntiles; t++) search_tile(S, sbase, lp, t, first_ctile, D, chunk, n_s, np, lane, warp == 28u);
         }
     }
 }

@@ -8,7 +8,7 @@ extern "C" {
 #endif
 
 #define GZM_HBITS       14
-#define GZM_H3BITS      12                        /* single-entry table of most recent 3-byte twins */
+#define GZM_H3BITS      11                        /* single-entry table of most recent 3-byte twins */
 #define GZM_H4BITS      12                        /* single-entry table of most recent 4-byte twins */
 #define GZM_SCAN_MIN    4096                      /* k_scan: shorter chunks always take the normal path       */
 #define GZM_SCAN_SAMPLE 256                       /* one 16-byte word per 256 bytes goes into the histogram   */

@@ -17,5 +17,5 @@ for level in levels:
     tiles = buf[7] or 1
     print(f"L{level} {kind} lz77 {ctx.stage_ms()['lz77']:.2f} ms ratio {n/r.out_bytes:.3f} | cycles per tile: "
           f"insert6={buf[8]/tiles:.0f} insert3={buf[9]/tiles:.0f} insert4={buf[10]/tiles:.0f} parse+emit={buf[11]/tiles:.0f}"
-          f" | search warp 0: search={buf[0]/tiles:.0f} waits: counter slot={buf[1]/tiles:.0f} tile inserted={buf[2]/tiles:.0f} tile parsed={buf[3]/tiles:.0f}"
+          f" | search warp 28: search={buf[0]/tiles:.0f} waits: counter slot={buf[1]/tiles:.0f} tile inserted={buf[2]/tiles:.0f} tile parsed={buf[3]/tiles:.0f}"
           f" | parse phases (thread 0): window exits={buf[12]/tiles:.0f} hop={buf[13]/tiles:.0f} marks={buf[14]/tiles:.0f} prefix+emit={buf[15]/tiles:.0f}", flush=True)
