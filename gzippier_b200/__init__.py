@@ -12,6 +12,8 @@ LIB_PATH = os.path.join(_HERE, "libgzb200.so")
 CORPUS_LIB_PATH = os.path.join(_HERE, "libgzbcorpus.so")     # input generator for bench / tests, separate from the engine
 
 OK, E_ARG, E_LEVEL, E_NOMEM, E_CUDA, E_NO_DEVICE, E_OUT_FULL, E_IO, E_VERIFY = 0, -1, -2, -3, -4, -5, -6, -7, -8
+E_TOO_LARGE = -9
+NOALLOC_MAX_BYTES = 8 << 30            # gzb_crc32_device_noalloc
 F_FINAL, F_RSYNCABLE, F_VERIFY = 1, 2, 4
 CHUNK, DICT, RSYNC_CHUNK = 131072, 32768, 16384
 CORPUS = {"text": 0, "zipf": 1, "binary": 2, "random": 3, "mixed": 4}
@@ -66,6 +68,7 @@ def lib():
         L.gzb_deflate_host.argtypes = [vp, i32, u32, vp, u64, vp, vp, u64, ctypes.POINTER(Result)]
         L.gzb_crc32_device.argtypes = [vp, u32, vp, u64, ctypes.POINTER(u32), vp]
         L.gzb_crc32_host.argtypes = [vp, u32, vp, u64, ctypes.POINTER(u32)]
+        L.gzb_crc32_device_noalloc.argtypes = [u32, vp, u64, vp, vp]
         L.gzb_crc32_combine.argtypes = [u32, u32, u64]; L.gzb_crc32_combine.restype = u32
         L.gzb_gzip_header.argtypes = [i32, u32, ctypes.c_char_p, vp, ctypes.c_size_t]
         L.gzb_gzip_trailer.argtypes = [u32, u64, vp, ctypes.c_size_t]
@@ -74,6 +77,14 @@ def lib():
         L.gzb_deflate_host_multi.argtypes = [ctypes.POINTER(vp), i32, i32, u32, vp, u64, vp, vp, u64, ctypes.POINTER(Result), ctypes.POINTER(Shard), i32]
         _lib = L
     return _lib
+
+
+def crc32_device_noalloc(d_in, n: int, d_crc_out, crc: int = 0, stream: int = 0) -> None:
+    """gzb_crc32_device_noalloc (include/gzb200.h): CRC-32 of n device bytes into the device word d_crc_out, on the current
+    device, with no allocation.  Enqueues and returns; n <= NOALLOC_MAX_BYTES.  No counterpart in the reference."""
+    rc = lib().gzb_crc32_device_noalloc(crc, _ptr(d_in), n, _ptr(d_crc_out), stream or None)
+    if rc != 0:
+        raise GzbError(rc, lib().gzb_strerror(rc).decode())
 
 
 def bound(n: int, flags: int = 0) -> int:

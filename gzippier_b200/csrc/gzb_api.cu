@@ -145,6 +145,7 @@ const char* gzb_strerror(int code)
     case GZB_E_OUT_FULL: return "output buffer smaller than gzb_bound()";
     case GZB_E_IO: return "I/O error";
     case GZB_E_VERIFY: return "GZB_F_VERIFY: the output does not decode back to the input";
+    case GZB_E_TOO_LARGE: return "input larger than GZB_NOALLOC_MAX_BYTES (the no-allocation entry point's static scratch)";
     default: return "unknown error";
     }
 }

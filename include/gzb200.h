@@ -37,6 +37,7 @@ extern "C" {
 #define GZB_E_OUT_FULL   (-6)   /* out_cap < gzb_bound(n)                               */
 #define GZB_E_IO         (-7)   /* read()/write() failed in the host driver             */
 #define GZB_E_VERIFY     (-8)   /* GZB_F_VERIFY: the output did not decode back to the input */
+#define GZB_E_TOO_LARGE  (-9)   /* gzb_crc32_device_noalloc: n > GZB_NOALLOC_MAX_BYTES  */
 
 /* ---- the reference's chunk grid (src/parallel.c:13-15) ---- */
 #define GZB_CHUNK        131072u   /* IN_BUF_SIZE                                       */
@@ -142,6 +143,19 @@ int gzb_deflate_host_multi(gzb_ctx **ctx, int n_ctx, int level, uint32_t flags,
 int gzb_crc32_device(gzb_ctx *ctx, uint32_t crc, const uint8_t *d_in, uint64_t n,
                      uint32_t *crc_out, void *stream);
 int gzb_crc32_host(gzb_ctx *ctx, uint32_t crc, const uint8_t *in, uint64_t n, uint32_t *crc_out);
+
+/* The same CRC-32 with no allocation of any kind.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Needs no gzb_ctx.  The per-chunk values live in a file-scope __device__ array
+ * (~260 KiB per GPU that loads the library, held until exit), which bounds the input: n <= GZB_NOALLOC_MAX_BYTES
+ * (8 GiB), else GZB_E_TOO_LARGE and nothing is launched.  Works on the CURRENT device, which must own d_in
+ * (16-byte aligned) and d_crc_out (a DEVICE word, written on `stream`; NULL = the default stream).  The call
+ * enqueues one 4-byte memset and one kernel and returns without synchronising.  Every call on a GPU shares the
+ * array: calls that overlap on the same GPU (two streams, two threads) race -- serialise them.  The first call
+ * on a device uploads 4 KiB of tables synchronously: make it (n = 0 will do) before starting a capture. */
+#define GZB_NOALLOC_MAX_BYTES 0x200000000ull
+int gzb_crc32_device_noalloc(uint32_t crc, const uint8_t *d_in, uint64_t n,
+                             uint32_t *d_crc_out, void *stream);
 
 /* CRC(A||B) from CRC(A), CRC(B), len(B) (replaces crc32_comb,
  * src/parallel.c:393-474 == lib/zlib/crc32.c:344-425).  Host arithmetic. */
