@@ -64,6 +64,9 @@ struct gzb_ctx {
     uint64_t dev_in_cap = 0, dev_out_cap = 0, pin_in_cap = 0, pin_out_cap = 0;
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t e_in[2] = {nullptr, nullptr}, e_cmp[2] = {nullptr, nullptr}, e_out[2] = {nullptr, nullptr};
+    // gzb_internal_blocking_sync (the fd driver's workers): the host waits of gzb_deflate_host sleep on these instead of spinning
+    cudaEvent_t e_blk_cmp = nullptr, e_blk_out[2] = {nullptr, nullptr};
+    bool blocking = false;
     char      err[512];
     std::mutex mu;
 };
@@ -213,7 +216,9 @@ int gzb_create(int device, gzb_ctx** out)
     for (int i = 0; ok && i < 2; i++)
         ok = cudaEventCreateWithFlags(&ctx->e_in[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&ctx->e_cmp[i], cudaEventDisableTiming) == cudaSuccess &&
-             cudaEventCreateWithFlags(&ctx->e_out[i], cudaEventDisableTiming) == cudaSuccess;
+             cudaEventCreateWithFlags(&ctx->e_out[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->e_blk_out[i], cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&ctx->e_blk_cmp, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
     if (!ok) { (void)cudaGetLastError(); gzb_destroy(ctx); return GZB_E_CUDA; }
     *out = ctx;
     return GZB_OK;
@@ -236,6 +241,8 @@ void gzb_destroy(gzb_ctx* ctx)
         if (ctx->e_in[i]) cudaEventDestroy(ctx->e_in[i]);
         if (ctx->e_cmp[i]) cudaEventDestroy(ctx->e_cmp[i]);
         if (ctx->e_out[i]) cudaEventDestroy(ctx->e_out[i]);
+        if (ctx->e_blk_out[i]) cudaEventDestroy(ctx->e_blk_out[i]);
+        if (i == 0 && ctx->e_blk_cmp) cudaEventDestroy(ctx->e_blk_cmp);
     }
     if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
     if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
@@ -575,7 +582,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     };
     auto drain = [&](int sl) -> int {                                      // complete the D2H of a slot
         if (!pend[sl].live) return GZB_OK;
-        CU(ctx, cudaEventSynchronize(ctx->e_out[sl]));
+        CU(ctx, cudaEventSynchronize(ctx->blocking ? ctx->e_blk_out[sl] : ctx->e_out[sl]));
         if (!pin_out) memcpy(out + pend[sl].opos, ctx->h_out[sl], pend[sl].bytes);
         pend[sl].live = false;
         return GZB_OK;
@@ -594,7 +601,8 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
             if (r != GZB_OK) return r;
             CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
             if (i + 1 < nbatch && (r = issue_h2d(i + 1)) != GZB_OK) return r; // overlaps the kernels of batch i
-            CU(ctx, cudaStreamSynchronize(ctx->stream));                    // out_bytes of batch i is known now
+            if (ctx->blocking) { CU(ctx, cudaEventRecord(ctx->e_blk_cmp, ctx->stream)); CU(ctx, cudaEventSynchronize(ctx->e_blk_cmp)); }
+            else CU(ctx, cudaStreamSynchronize(ctx->stream));               // out_bytes of batch i is known now
             const Cursor c = *ctx->h_cursor;
             if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
             if (c.verify_bad) return verify_status(ctx, c);
@@ -602,6 +610,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
             if (opos + c.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
             if (c.out_bytes) CU(ctx, cudaMemcpyAsync(pin_out ? out + opos : ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));
             CU(ctx, cudaEventRecord(ctx->e_out[sl], ctx->s_out));
+            if (ctx->blocking) CU(ctx, cudaEventRecord(ctx->e_blk_out[sl], ctx->s_out));
             pend[sl].bytes = c.out_bytes; pend[sl].opos = opos; pend[sl].live = true;
             opos += c.out_bytes;
             total.crc32 = gzb_crc32_combine(total.crc32, c.crc, nb);
@@ -709,6 +718,14 @@ static int crc32_device_locked(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, 
     }
     *crc_out = acc;
     return GZB_OK;
+}
+
+// internal (host/gzb_zip.c; not declared in gzb200.h): with `on`, the host-side waits of gzb_deflate_host use blocking events
+void gzb_internal_blocking_sync(gzb_ctx* ctx, int on)
+{
+    if (!ctx) return;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->blocking = on != 0 && ctx->e_blk_cmp != nullptr;
 }
 
 int gzb_crc32_device(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, uint64_t n, uint32_t* crc_out, void* stream)

@@ -14,6 +14,9 @@
  *   writer   (one thread)       header, fragments in batch order, CRCs folded with
  *                               crc32_combine (:544), trailer (:496-507, :538, :555-556)
  *
+ * Between two regular files none of this is serial (zip_direct below): every worker reads its own batches and writes its
+ * fragments at their final offsets, the copies spread over one I/O thread per CPU.
+ *
  * Batches are independent given their dictionary, so with n_gpus > 1 consecutive batches simply
  * go to different GPUs: contiguous shards on chunk boundaries, no collective.
  * With opts->members every batch is closed as a gzip member of its own (no dictionary across batches): the
@@ -32,6 +35,9 @@
 #include <sys/stat.h>
 #include <time.h>
 #include <unistd.h>
+
+/* not part of the public ABI (gzb_api.cu): waits inside gzb_deflate_host sleep on blocking events instead of spinning */
+void gzb_internal_blocking_sync(gzb_ctx *ctx, int on);
 
 #define MAX_GPUS 16
 #define MAX_WORKERS (2 * MAX_GPUS)
@@ -264,19 +270,191 @@ void gzb_zip_release(void)
     g_pool.nctx = g_pool.ng = 0;
     pthread_mutex_unlock(&g_pool.mu);
 }
-/* contexts for 2 workers on each of ng GPUs (worker w on GPU w % ng); the pool's lock is held */
-static int pool_contexts(int ng)
+/* contexts for wpg workers on each of ng GPUs (worker w on GPU w % ng); the pool's lock is held */
+static int pool_contexts(int ng, int wpg)
 {
     if (g_pool.ng != ng) {
         for (int w = 0; w < g_pool.nctx; w++) { gzb_destroy(g_pool.ctx[w]); g_pool.ctx[w] = NULL; }
         g_pool.nctx = 0; g_pool.ng = ng;
     }
-    while (g_pool.nctx < 2 * ng) {
+    while (g_pool.nctx < wpg * ng) {
         int rc = gzb_create(g_pool.nctx % ng, &g_pool.ctx[g_pool.nctx]);
         if (rc != GZB_OK) return rc;
         g_pool.nctx++;
     }
     return GZB_OK;
+}
+
+/* ---- file to file ------------------------------------------------------------------------------------------------
+ * When both ends are regular files nothing has to pass through ONE reader and ONE writer: batch i is the bytes
+ * [base + i * BATCH, ...) of the input, its dictionary the 32 KiB in front of them, and its place in the output is known
+ * as soon as the sizes of the batches before it are.  So every worker takes the next batch, reads it (dictionary included,
+ * one contiguous range) into its own pinned slot, compresses it and writes the fragment at its offset; the copies between
+ * page cache and slots are cut into pieces and done by a pool of I/O threads (one per CPU) that all workers share.  The
+ * serial reader / in-order writer above remain for pipes, terminals, append-mode output and the member-per-batch mode. */
+#define IO_PIECE ((size_t)2 << 20)
+#define IO_QUEUE 8192
+#define IO_MAX_THREADS 128
+typedef struct { int pending, rc; } io_group;
+typedef struct { int fd, wr; uint8_t *buf; size_t len; off_t off; io_group *grp; } io_piece;
+typedef struct {
+    pthread_mutex_t mu; pthread_cond_t work, done;
+    io_piece q[IO_QUEUE]; unsigned head, tail;      /* head: next to take, tail: next free */
+    int stop, nth; pthread_t th[IO_MAX_THREADS];
+} io_pool;
+
+static void *io_thread(void *arg)
+{
+    io_pool *io = (io_pool *)arg;
+    pthread_mutex_lock(&io->mu);
+    for (;;) {
+        while (io->head == io->tail && !io->stop) pthread_cond_wait(&io->work, &io->mu);
+        if (io->head == io->tail) break;
+        io_piece pc = io->q[io->head++ % IO_QUEUE];
+        pthread_mutex_unlock(&io->mu);
+        int rc = 0; size_t done = 0;
+        while (done < pc.len) {
+            ssize_t r = pc.wr ? pwrite(pc.fd, pc.buf + done, pc.len - done, pc.off + (off_t)done)
+                              : pread(pc.fd, pc.buf + done, pc.len - done, pc.off + (off_t)done);
+            if (r < 0 && errno == EINTR) continue;
+            if (r <= 0) { rc = -1; break; }        /* a short file is an error here: its size was taken at the start */
+            done += (size_t)r;
+        }
+        pthread_mutex_lock(&io->mu);
+        if (rc) pc.grp->rc = rc;
+        if (--pc.grp->pending == 0) pthread_cond_broadcast(&io->done);
+    }
+    pthread_mutex_unlock(&io->mu);
+    return NULL;
+}
+
+/* copy [off, off + len) of fd to / from buf on the pool; returns when all of it is done */
+static int io_run(io_pool *io, int fd, int wr, uint8_t *buf, size_t len, off_t off)
+{
+    io_group g = { 0, 0 };
+    pthread_mutex_lock(&io->mu);
+    for (size_t o = 0; o < len; o += IO_PIECE) {
+        while (io->tail - io->head == IO_QUEUE) pthread_cond_wait(&io->done, &io->mu);     /* full: never in practice */
+        io_piece *pc = &io->q[io->tail++ % IO_QUEUE];
+        pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->len = len - o < IO_PIECE ? len - o : IO_PIECE; pc->off = off + (off_t)o; pc->grp = &g;
+        g.pending++;
+    }
+    pthread_cond_broadcast(&io->work);
+    while (g.pending) pthread_cond_wait(&io->done, &io->mu);
+    pthread_mutex_unlock(&io->mu);
+    return g.rc;
+}
+
+typedef struct {
+    pthread_mutex_t mu; pthread_cond_t cv;
+    io_pool *io;
+    int ifd, ofd, level, rc; uint32_t flags;
+    off_t base, obase;                 /* first input byte; first output byte after the header */
+    uint64_t n, batch, dict_sz, out_cap, nb;
+    uint64_t next;                     /* next batch to hand out */
+    uint64_t known;                    /* batches [0, known) have their sizes in; pre[known] is final */
+    uint64_t *pre;                     /* pre[i] = bytes of the fragments before batch i  (nb + 1 entries) */
+    uint64_t *size; uint32_t *crc; uint8_t *have;
+    gzb_ctx *ctx[MAX_WORKERS];
+} direct_t;
+typedef struct { direct_t *d; int w; } direct_arg;
+
+static void direct_fail(direct_t *d, int rc)
+{
+    pthread_mutex_lock(&d->mu);
+    if (d->rc == GZB_OK) d->rc = rc;
+    pthread_cond_broadcast(&d->cv);
+    pthread_mutex_unlock(&d->mu);
+}
+
+static void *direct_worker(void *arg)
+{
+    direct_t *d = ((direct_arg *)arg)->d;
+    const int w = ((direct_arg *)arg)->w;
+    uint8_t *in = g_pool.in[w], *out = g_pool.out[w];                    /* slot w is this worker's */
+    if (!in) {                                                            /* page-locked on first use, kept by the pool */
+        int rc = gzb_host_alloc(d->ctx[w], GZB_DICT + d->batch, (void **)&in);
+        g_pool.in[w] = in;
+        if (rc == GZB_OK) { rc = gzb_host_alloc(d->ctx[w], d->out_cap, (void **)&out); g_pool.out[w] = out; }
+        if (rc != GZB_OK) { direct_fail(d, rc); return NULL; }
+    }
+    for (;;) {
+        pthread_mutex_lock(&d->mu);
+        const uint64_t i = d->next;
+        const int stop = d->rc != GZB_OK || i >= d->nb;
+        if (!stop) d->next = i + 1;
+        pthread_mutex_unlock(&d->mu);
+        if (stop) return NULL;
+        const uint64_t off = i * d->batch, len = d->n - off < d->batch ? d->n - off : d->batch;
+        const uint64_t dict = i > 0 ? d->dict_sz : 0;                     /* the bytes in front of the batch are its dictionary */
+        uint8_t *data = in + GZB_DICT;
+        if (io_run(d->io, d->ifd, 0, data - dict, (size_t)(dict + len), d->base + (off_t)(off - dict))) { direct_fail(d, GZB_E_IO); return NULL; }
+        gzb_result res;
+        int rc = gzb_deflate_host(d->ctx[w], d->level, d->flags | (i + 1 == d->nb ? GZB_F_FINAL : 0u), data, len,
+                                  dict ? data - dict : NULL, out, d->out_cap, &res);
+        if (rc != GZB_OK) { direct_fail(d, rc); return NULL; }
+        pthread_mutex_lock(&d->mu);
+        d->size[i] = res.out_bytes; d->crc[i] = res.crc32; d->have[i] = 1;
+        while (d->known < d->nb && d->have[d->known]) { d->pre[d->known + 1] = d->pre[d->known] + d->size[d->known]; d->known++; }
+        pthread_cond_broadcast(&d->cv);
+        /* batches are handed out in order and a worker publishes its size before it waits: the oldest one never waits */
+        while (d->rc == GZB_OK && d->known < i) pthread_cond_wait(&d->cv, &d->mu);
+        const int bad = d->rc != GZB_OK;
+        const uint64_t at = d->pre[i];
+        pthread_mutex_unlock(&d->mu);
+        if (bad) return NULL;
+        if (io_run(d->io, d->ofd, 1, out, (size_t)res.out_bytes, d->obase + (off_t)at)) { direct_fail(d, GZB_E_IO); return NULL; }
+    }
+}
+
+/* the body of a member, file to file: n input bytes at base -> fragments from obase on.  The pool's lock is held. */
+static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw, off_t base, uint64_t n, off_t obase,
+                      uint64_t batch, uint64_t out_cap, uint32_t *crc_out, uint64_t *out_bytes)
+{
+    static io_pool io;                                                    /* one call at a time (g_pool.mu) */
+    direct_t D, *d = &D;
+    memset(d, 0, sizeof(*d)); memset(&io, 0, sizeof(io));
+    d->ifd = ifd; d->ofd = ofd; d->level = o->level; d->flags = flags; d->base = base; d->obase = obase; d->n = n;
+    d->batch = batch; d->out_cap = out_cap; d->dict_sz = (flags & GZB_F_RSYNCABLE) ? 0 : GZB_DICT;
+    d->nb = (n + batch - 1) / batch; d->rc = GZB_OK; d->io = &io;
+    for (int w = 0; w < nw; w++) d->ctx[w] = g_pool.ctx[w];
+    d->pre = (uint64_t *)calloc(d->nb + 1, sizeof(uint64_t)); d->size = (uint64_t *)calloc(d->nb, sizeof(uint64_t));
+    d->crc = (uint32_t *)calloc(d->nb, sizeof(uint32_t)); d->have = (uint8_t *)calloc(d->nb, 1);
+    int rc = (d->pre && d->size && d->crc && d->have) ? GZB_OK : GZB_E_NOMEM;
+    pthread_mutex_init(&d->mu, NULL); pthread_cond_init(&d->cv, NULL);
+    pthread_mutex_init(&io.mu, NULL); pthread_cond_init(&io.work, NULL); pthread_cond_init(&io.done, NULL);
+    long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+    int want = ncpu > 0 ? (int)ncpu : 8;
+    { const char *e = getenv("GZB_ZIP_IO_THREADS"); if (e && atoi(e) > 0) want = atoi(e); }
+    if (want > IO_MAX_THREADS) want = IO_MAX_THREADS;
+    pthread_t th[MAX_WORKERS]; direct_arg wa[MAX_WORKERS]; int nth = 0;
+    if (rc == GZB_OK) {
+        for (; io.nth < want; io.nth++) if (pthread_create(&io.th[io.nth], NULL, io_thread, &io)) break;
+        if (io.nth == 0) rc = GZB_E_NOMEM;
+    }
+    if (rc == GZB_OK) {
+        for (int w = 0; w < nw; w++) {
+            wa[w].d = d; wa[w].w = w;
+            if (pthread_create(&th[w], NULL, direct_worker, &wa[w])) { direct_fail(d, GZB_E_NOMEM); break; }
+            nth++;
+        }
+        for (int w = 0; w < nth; w++) pthread_join(th[w], NULL);
+        rc = d->rc;
+    }
+    pthread_mutex_lock(&io.mu); io.stop = 1; pthread_cond_broadcast(&io.work); pthread_mutex_unlock(&io.mu);
+    for (int k = 0; k < io.nth; k++) pthread_join(io.th[k], NULL);
+    if (rc == GZB_OK) {
+        uint32_t crc = 0;
+        for (uint64_t i = 0; i < d->nb; i++) {
+            const uint64_t off = i * batch, len = n - off < batch ? n - off : batch;
+            crc = gzb_crc32_combine(crc, d->crc[i], len);                 /* src/parallel.c:544 */
+        }
+        *crc_out = crc; *out_bytes = d->pre[d->nb];
+    }
+    free(d->pre); free(d->size); free(d->crc); free(d->have);
+    pthread_mutex_destroy(&d->mu); pthread_cond_destroy(&d->cv);
+    pthread_mutex_destroy(&io.mu); pthread_cond_destroy(&io.work); pthread_cond_destroy(&io.done);
+    return rc;
 }
 
 /* Inputs that end within SMALL bytes -- most files a gzip ever sees -- take one call on pageable memory: no pinned
@@ -316,6 +494,7 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     struct stat st;
     off_t pos = 0;
     const int regular = fstat(ifd, &st) == 0 && S_ISREG(st.st_mode) && (pos = lseek(ifd, 0, SEEK_CUR)) >= 0;
+    const uint64_t in_left = regular && st.st_size > pos ? (uint64_t)(st.st_size - pos) : 0;   /* as of now: a file that grows meanwhile is cut here */
     /* a regular output file that is not in append mode is written with pwrite at explicit offsets */
     const int oflags = fcntl(ofd, F_GETFL);
     p->out_regular = fstat(ofd, &st) == 0 && S_ISREG(st.st_mode) && oflags >= 0 && !(oflags & O_APPEND) && (p->opos = lseek(ofd, 0, SEEK_CUR)) >= 0;
@@ -344,12 +523,36 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
     if (write_batch(ofd, hdr, (size_t)hn, p->out_regular, &p->opos)) { rc = GZB_E_IO; goto done; }
     o->bytes_in = 0; o->bytes_out = (uint64_t)hn;
 
+    /* file to file, and more than a small input: no serial stage at all (zip_direct) */
+    if (regular && p->out_regular && !o->members && in_left > SMALL && !getenv("GZB_ZIP_NO_DIRECT")) {
+        /* a worker reads, compresses and writes one batch after the other: four of them per GPU keep its kernels back to back */
+        int wpg = 4;
+        { const char *e = getenv("GZB_ZIP_WORKERS_PER_GPU"); if (e && atoi(e) > 0) wpg = atoi(e); }
+        if (wpg * ng > MAX_WORKERS) wpg = MAX_WORKERS / ng;
+        { const uint64_t nb = (in_left + p->batch - 1) / p->batch; while (wpg > 1 && (uint64_t)(wpg - 1) * (uint64_t)ng >= nb) wpg--; }
+        const int nw = wpg * ng;
+        if ((rc = pool_contexts(ng, wpg)) != GZB_OK) goto done;
+        if (g_pool.batch != p->batch || g_pool.out_cap != p->out_cap) { pool_free_slots(); g_pool.batch = p->batch; g_pool.out_cap = p->out_cap; }
+        for (int w = 0; w < nw; w++) gzb_internal_blocking_sync(g_pool.ctx[w], 1);             /* waiting workers leave their CPUs to the I/O threads */
+        t_setup = now_s();
+        uint32_t crc = 0; uint64_t ob = 0; uint8_t tr[8];
+        rc = zip_direct(ifd, ofd, o, p->flags, nw, pos, in_left, p->opos, p->batch, p->out_cap, &crc, &ob);
+        for (int w = 0; w < nw; w++) gzb_internal_blocking_sync(g_pool.ctx[w], 0);
+        if (rc == GZB_OK) {
+            pos += (off_t)in_left; p->opos += (off_t)ob; o->bytes_in = in_left; o->bytes_out += ob;
+            gzb_gzip_trailer(crc, in_left, tr, sizeof(tr));
+            if (write_batch(ofd, tr, 8, 1, &p->opos)) rc = GZB_E_IO; else o->bytes_out += 8;
+        }
+        t_stream = now_s();
+        goto done;
+    }
+
     /* look at the first SMALL bytes: is that all there is? */
     const size_t peek_len = SMALL < p->batch ? SMALL : (size_t)p->batch;
     if (!(peek = (uint8_t *)malloc(peek_len))) { rc = GZB_E_NOMEM; goto done; }
     ssize_t pk = read_batch(ifd, peek, peek_len, regular, &pos);
     if (pk < 0) { rc = GZB_E_IO; goto done; }
-    if ((rc = pool_contexts(ng)) != GZB_OK) goto done;
+    if ((rc = pool_contexts(ng, 2)) != GZB_OK) goto done;
     for (int w = 0; w < p->nworkers; w++) p->ctx[w] = g_pool.ctx[w];
     if ((size_t)pk < peek_len) {
         if (p->out_regular) lseek(ofd, p->opos, SEEK_SET);          /* the small path writes sequentially */

@@ -335,8 +335,14 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
     d = gz.corpus("mixed", n, seed=41)
     want = orc.engine_model(d, 6).tobytes()
     src = tmp_path / "big.bin"; src.write_bytes(d.tobytes())
-    for mb in ("1", "3", "128"):
+    # file to file takes the path without a serial stage (every worker reads its own batches and writes its fragments at
+    # their offsets); GZB_ZIP_NO_DIRECT=1 keeps the one-reader / in-order-writer pipeline that pipes use
+    for mb, serial in (("1", False), ("3", False), ("128", False), ("1", True), ("5", True)):
         monkeypatch.setenv("GZB_ZIP_BATCH_MB", mb)
+        if serial:
+            monkeypatch.setenv("GZB_ZIP_NO_DIRECT", "1")
+        else:
+            monkeypatch.delenv("GZB_ZIP_NO_DIRECT", raising=False)
         dst = tmp_path / f"out{mb}.gz"
         with open(src, "rb") as fi, open(dst, "wb") as fo:
             bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
@@ -344,6 +350,7 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
         m = dst.read_bytes()
         assert bi == n and bo == len(m)
         assert m[:10] == gz.gzip_header(6) and m[10:-8] == want and m[-8:] == gz.gzip_trailer(zlib.crc32(d.tobytes()), n)
+    monkeypatch.delenv("GZB_ZIP_NO_DIRECT", raising=False)
     # the contexts and pinned slots of the last call are still in the pool: the same call again, then an explicit release
     with open(src, "rb") as fi, open(dst, "wb") as fo:
         bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), level=6)
