@@ -4,6 +4,7 @@
 // where its buffer pools stand (:327-347).  Everything here is plumbing; the arithmetic is in k_*.cu.
 #include "gzb_common.cuh"
 #include "gzb200.h"
+#include "gzb_internal.h"
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -64,9 +65,8 @@ struct gzb_ctx {
     uint64_t dev_in_cap = 0, dev_out_cap = 0, pin_in_cap = 0, pin_out_cap = 0;
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t e_in[2] = {nullptr, nullptr}, e_cmp[2] = {nullptr, nullptr}, e_out[2] = {nullptr, nullptr};
-    // gzb_internal_blocking_sync (the fd driver's workers): the host waits of gzb_deflate_host sleep on these instead of spinning
-    cudaEvent_t e_blk_cmp = nullptr, e_blk_out[2] = {nullptr, nullptr};
-    bool blocking = false;
+    // gzb_internal_deflate_batches with `blocking` (the fd driver's workers): the host waits sleep on these instead of spinning
+    cudaEvent_t e_blk_cmp = nullptr, e_blk_in = nullptr, e_blk_out[2] = {nullptr, nullptr};
     char      err[512];
     std::mutex mu;
 };
@@ -218,7 +218,8 @@ int gzb_create(int device, gzb_ctx** out)
              cudaEventCreateWithFlags(&ctx->e_cmp[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&ctx->e_out[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&ctx->e_blk_out[i], cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
-    ok = ok && cudaEventCreateWithFlags(&ctx->e_blk_cmp, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&ctx->e_blk_cmp, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess
+            && cudaEventCreateWithFlags(&ctx->e_blk_in, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
     if (!ok) { (void)cudaGetLastError(); gzb_destroy(ctx); return GZB_E_CUDA; }
     *out = ctx;
     return GZB_OK;
@@ -243,6 +244,7 @@ void gzb_destroy(gzb_ctx* ctx)
         if (ctx->e_out[i]) cudaEventDestroy(ctx->e_out[i]);
         if (ctx->e_blk_out[i]) cudaEventDestroy(ctx->e_blk_out[i]);
         if (i == 0 && ctx->e_blk_cmp) cudaEventDestroy(ctx->e_blk_cmp);
+        if (i == 0 && ctx->e_blk_in) cudaEventDestroy(ctx->e_blk_in);
     }
     if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
     if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
@@ -582,7 +584,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
     };
     auto drain = [&](int sl) -> int {                                      // complete the D2H of a slot
         if (!pend[sl].live) return GZB_OK;
-        CU(ctx, cudaEventSynchronize(ctx->blocking ? ctx->e_blk_out[sl] : ctx->e_out[sl]));
+        CU(ctx, cudaEventSynchronize(ctx->e_out[sl]));
         if (!pin_out) memcpy(out + pend[sl].opos, ctx->h_out[sl], pend[sl].bytes);
         pend[sl].live = false;
         return GZB_OK;
@@ -601,8 +603,7 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
             if (r != GZB_OK) return r;
             CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
             if (i + 1 < nbatch && (r = issue_h2d(i + 1)) != GZB_OK) return r; // overlaps the kernels of batch i
-            if (ctx->blocking) { CU(ctx, cudaEventRecord(ctx->e_blk_cmp, ctx->stream)); CU(ctx, cudaEventSynchronize(ctx->e_blk_cmp)); }
-            else CU(ctx, cudaStreamSynchronize(ctx->stream));               // out_bytes of batch i is known now
+            CU(ctx, cudaStreamSynchronize(ctx->stream));                    // out_bytes of batch i is known now
             const Cursor c = *ctx->h_cursor;
             if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
             if (c.verify_bad) return verify_status(ctx, c);
@@ -610,7 +611,6 @@ int gzb_deflate_host(gzb_ctx* ctx, int level, uint32_t flags, const uint8_t* in,
             if (opos + c.out_bytes > out_cap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
             if (c.out_bytes) CU(ctx, cudaMemcpyAsync(pin_out ? out + opos : ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));
             CU(ctx, cudaEventRecord(ctx->e_out[sl], ctx->s_out));
-            if (ctx->blocking) CU(ctx, cudaEventRecord(ctx->e_blk_out[sl], ctx->s_out));
             pend[sl].bytes = c.out_bytes; pend[sl].opos = opos; pend[sl].live = true;
             opos += c.out_bytes;
             total.crc32 = gzb_crc32_combine(total.crc32, c.crc, nb);
@@ -720,12 +720,103 @@ static int crc32_device_locked(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, 
     return GZB_OK;
 }
 
-// internal (host/gzb_zip.c; not declared in gzb200.h): with `on`, the host-side waits of gzb_deflate_host use blocking events
-void gzb_internal_blocking_sync(gzb_ctx* ctx, int on)
+// internal (gzb_internal.h): batches through callbacks, for the fd driver.  One thread per context.
+int gzb_internal_deflate_batches(gzb_ctx* ctx, int level, uint32_t flags, const gzb_batch_io* io)
 {
-    if (!ctx) return;
+    if (!ctx || !io || !io->fetch || !io->emit) return GZB_E_ARG;
+    if (level < 1 || level > 9) return fail(ctx, GZB_E_LEVEL, "level must be 1..9");
+    const uint32_t dsz = (flags & GZB_F_RSYNCABLE) ? 0u : GZB_DICT;
     std::lock_guard<std::mutex> g(ctx->mu);
-    ctx->blocking = on != 0 && ctx->e_blk_cmp != nullptr;
+    if (ctx->pending) return fail(ctx, GZB_E_ARG, "a device call is pending on this context: gzb_deflate_wait() first");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const uint64_t bmax = io->max_bytes, ocap = gzb_bound(bmax, flags);
+    int rc = ensure_dev(ctx, dsz + bmax + 16, ocap);
+    if (rc == GZB_OK) rc = ensure_pinned(ctx, dsz + bmax + 16, ocap);
+    if (rc != GZB_OK) return rc;
+    const bool blk = io->blocking != 0;
+    // live: the fragment is on its way to / in h_out and has not been emitted; busy: emitted, the caller may still read h_out
+    struct Slot { uint64_t len = 0; int have_dict = 0, final = 0; gzb_result res; bool live = false, busy = false; uint64_t k = 0; } slot[2];
+
+    auto wait_event = [&](cudaEvent_t spin, cudaEvent_t sleep, cudaStream_t st) -> cudaError_t {
+        if (!blk) return cudaEventSynchronize(spin);
+        cudaError_t e = cudaEventRecord(sleep, st);                         // behind `spin` on the same stream
+        return e != cudaSuccess ? e : cudaEventSynchronize(sleep);
+    };
+    auto fetch_h2d = [&](uint64_t k) -> int {                               // batch k into slot k & 1
+        const int sl = (int)(k & 1);
+        Slot& S = slot[sl];
+        CU(ctx, wait_event(ctx->e_in[sl], ctx->e_blk_in, ctx->s_in));      // the staging buffer's previous batch has left the host
+        uint8_t* hin = ctx->h_in[sl] + dsz;
+        S.len = 0; S.have_dict = 0; S.final = 0;
+        int r = io->fetch(io->user, k, hin, dsz, &S.len, &S.have_dict, &S.final);
+        if (r != GZB_OK) return fail(ctx, r, "fetch callback failed");
+        if (S.len > bmax) return fail(ctx, GZB_E_ARG, "fetch returned more than max_bytes");
+        const uint32_t halo = (S.have_dict && dsz) ? dsz : 0u;
+        CU(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->e_cmp[sl], 0));        // kernels of batch k-2 have read this device slot
+        if (halo + S.len) CU(ctx, cudaMemcpyAsync(ctx->d_in[sl] + (dsz - halo), hin - halo, halo + S.len, cudaMemcpyHostToDevice, ctx->s_in));
+        CU(ctx, cudaEventRecord(ctx->e_in[sl], ctx->s_in));
+        return GZB_OK;
+    };
+    auto emit_slot = [&](int sl) -> int {                                   // hand the fragment of a slot to the caller
+        Slot& S = slot[sl];
+        if (!S.live) return GZB_OK;
+        CU(ctx, wait_event(ctx->e_out[sl], ctx->e_blk_out[sl], ctx->s_out));
+        S.live = false; S.busy = io->emit_done != nullptr;
+        int r = io->emit(io->user, S.k, ctx->h_out[sl], &S.res);
+        return r == GZB_OK ? GZB_OK : fail(ctx, r, "emit callback failed");
+    };
+    auto release_slot = [&](int sl) -> int {                                // the caller is through with h_out[sl]
+        Slot& S = slot[sl];
+        if (!S.busy) return GZB_OK;
+        S.busy = false;
+        int r = io->emit_done(io->user, S.k);
+        return r == GZB_OK ? GZB_OK : fail(ctx, r, "emit_done callback failed");
+    };
+    auto pipeline = [&]() -> int {
+        int r;
+        if (io->n_batches == 0) return GZB_OK;
+        if ((r = fetch_h2d(0)) != GZB_OK) return r;
+        for (uint64_t k = 0; k < io->n_batches; k++) {
+            const int sl = (int)(k & 1);
+            Slot& S = slot[sl];
+            const uint32_t halo = (S.have_dict && dsz) ? dsz : 0u;
+            const uint32_t f = (flags & ~GZB_F_FINAL) | (S.final ? GZB_F_FINAL : 0u);
+            // the kernels go first: the device output slot is free once the D2H of batch k-2 is through (a wait on the GPU) ...
+            CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->e_in[sl], 0));
+            CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->e_out[sl], 0));
+            r = enqueue_deflate(ctx, level, f, ctx->d_in[sl] + dsz, S.len, halo, ctx->d_out[sl], ctx->dev_out_cap, ctx->stream);
+            if (r != GZB_OK) return r;
+            CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
+            // ... and under them the host passes on batch k-1 (its D2H was the last thing of the round before) and reads batch k+1
+            if ((r = emit_slot(sl ^ 1)) != GZB_OK) return r;
+            if (k + 1 < io->n_batches && (r = fetch_h2d(k + 1)) != GZB_OK) return r;
+            CU(ctx, wait_event(ctx->e_cmp[sl], ctx->e_blk_cmp, ctx->stream));   // out_bytes of batch k is known now
+            if ((r = release_slot(sl)) != GZB_OK) return r;                  // batch k-2 has left the pinned slot
+            const Cursor c = *ctx->h_cursor;
+            if (c.status != GZB_OK) return fail(ctx, c.status, "device pipeline reported an error");
+            if (c.verify_bad) return verify_status(ctx, c);
+            if (c.in_bytes != S.len) return fail(ctx, GZB_E_CUDA, "pipeline consumed a different number of bytes than submitted");
+            if (c.out_bytes > ocap) return fail(ctx, GZB_E_OUT_FULL, "output overflow");
+            if (c.out_bytes) CU(ctx, cudaMemcpyAsync(ctx->h_out[sl], ctx->d_out[sl], c.out_bytes, cudaMemcpyDeviceToHost, ctx->s_out));
+            CU(ctx, cudaEventRecord(ctx->e_out[sl], ctx->s_out));
+            memset(&S.res, 0, sizeof(S.res));
+            S.res.in_bytes = S.len; S.res.out_bytes = c.out_bytes; S.res.crc32 = c.crc; S.res.n_chunks = c.n_chunks; S.res.n_blocks = c.n_blocks;
+            S.k = k; S.live = true;
+        }
+        const int last = (int)((io->n_batches - 1) & 1);
+        if ((r = emit_slot(last)) != GZB_OK) return r;
+        if ((r = release_slot(last ^ 1)) != GZB_OK) return r;
+        return release_slot(last);
+    };
+    rc = pipeline();
+    if (rc != GZB_OK) {                                                     // as in gzb_deflate_host: nothing stays in flight
+        char keep[sizeof(ctx->err)]; memcpy(keep, ctx->err, sizeof(keep));
+        for (int sl = 0; sl < 2; sl++) if (slot[sl].busy) { slot[sl].busy = false; (void)io->emit_done(io->user, slot[sl].k); }
+        cudaStreamSynchronize(ctx->s_in); cudaStreamSynchronize(ctx->stream); cudaStreamSynchronize(ctx->s_out);
+        (void)cudaGetLastError();
+        memcpy(ctx->err, keep, sizeof(keep));
+    }
+    return rc;
 }
 
 int gzb_crc32_device(gzb_ctx* ctx, uint32_t crc, const uint8_t* d_in, uint64_t n, uint32_t* crc_out, void* stream)

@@ -31,6 +31,7 @@ namespace gzb {
 namespace {
 
 constexpr int SCAN_THREADS = 256;
+constexpr uint32_t GQ_CAP = 160;         // gram_scan's queue per warp: 31 left over + at most 4 * 32 new ones per step
 
 __device__ __forceinline__ uint32_t lg_q8(uint32_t x)            // 256 * log2(x), x >= 1
 {
@@ -46,6 +47,8 @@ struct ScanSmem {
     uint32_t s_len[SCAN_THREADS];
     uint32_t hist[SCAN_THREADS / 32][256];       // one byte histogram per warp
     uint32_t grams[SCAN_SLOTS];                  // fingerprints of the sampled 8-byte grams (0 = empty)
+    uint32_t gq[SCAN_THREADS / 32][GQ_CAP];      // per warp: sampled positions waiting to be fingerprinted (gram_scan)
+    uint32_t gqn[SCAN_THREADS / 32];
     unsigned long long bits_q8;                  // sum over byte values of count * (lg(n) - lg(count))
     uint32_t n_distinct, n_chunk_grams, n_chunk_new, overflow, verdict;
 };
@@ -68,37 +71,67 @@ __device__ __forceinline__ uint32_t gram_insert(ScanSmem& S, uint32_t fp)
     }
 }
 
-// the sampled positions among the four that start in aligned word q of the stream (m: see gram_scan)
-__device__ __forceinline__ void gram_word(ScanSmem& S, const uint32_t* w, uint32_t q, uint32_t w0, uint32_t m, uint32_t& ngram, uint32_t& nnew)
-{
-    const uint32_t w1 = __ldg(w + q + 1u), w2 = __ldg(w + q + 2u);
-#pragma unroll
-    for (uint32_t j = 0; j < 4u; j++) {
-        if (((m >> (8u * j)) & 0xFFu) == 0u) {
-            const uint32_t a = j ? __funnelshift_r(w0, w1, 8u * j) : w0, b = j ? __funnelshift_r(w1, w2, 8u * j) : w1;
-            ngram++; nnew += gram_insert(S, scan_fingerprint(a, b));
-        }
-    }
-}
 // Grams of the stream positions [p0, p1) (multiples of 4).  The first bytes of four consecutive positions are the bytes
-// of one aligned word, so one masked zero-byte test says whether any of the four is sampled (6 % of the words).  This is a
-// second pass over bytes that have partly left the caches: four independent loads are in flight per thread.
-// (Measured on B200: 16-byte loads with four tests per load are slower -- the rare path then runs in every warp step.)
+// of one aligned word, so one masked zero-byte test says whether any of the four is sampled (6 % of the words) -- but in
+// 86 % of the warp steps SOME lane has such a word, so handling it on the spot would run the long path (two more loads,
+// fingerprint, table insert) in nearly every step with one or two lanes active.  Instead the lanes only append the
+// sampled positions to a queue of their warp, and whenever 32 are waiting the warp handles them with all lanes busy.
+// This is a second pass over bytes that have partly left the caches: four independent loads are in flight per thread.
+// (Measured on B200: 16-byte loads with four tests per load are slower.)  The result is a set and two counts: the order
+// in which positions reach the table does not matter.
+
+__device__ __forceinline__ void gram_take(ScanSmem& S, const uint8_t* sp, uint32_t p, uint32_t& ngram, uint32_t& nnew)
+{
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(sp + (p & ~3u));
+    const uint32_t sh = (p & 3u) * 8u;
+    const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    const uint32_t a = sh ? __funnelshift_r(w0, w1, sh) : w0, b = sh ? __funnelshift_r(w1, w2, sh) : w1;
+    ngram++; nnew += gram_insert(S, scan_fingerprint(a, b));
+}
+
 __device__ void gram_scan(ScanSmem& S, const uint8_t* sp, uint32_t p0, uint32_t p1, bool count, uint32_t tid)
 {
     uint32_t ngram = 0, nnew = 0;
+    const uint32_t lane = tid & 31u, warp = tid >> 5;
     const uint32_t* w = reinterpret_cast<const uint32_t*>(sp);
     const uint32_t qe = p1 / 4u;
-    auto test = [&](uint32_t q, uint32_t w0) {
-        const uint32_t m = (w0 & 0x3F3F3F3Fu) ^ 0x2A2A2A2Au;                 // a zero byte <=> that position is sampled
-        if (((m - 0x01010101u) & ~m & 0x80808080u) != 0u) gram_word(S, w, q, w0, m, ngram, nnew);
+    uint32_t* Q = S.gq[warp];
+    uint32_t* qn = &S.gqn[warp];
+    if (lane == 0) *qn = 0;
+    __syncwarp();
+    auto test = [&](uint32_t q, uint32_t w0, bool live) {        // whole warp; live: this lane's word exists
+        const uint32_t m = (w0 & 0x3F3F3F3Fu) ^ 0x2A2A2A2Au;     // a zero byte <=> that position is sampled
+        if (live && ((m - 0x01010101u) & ~m & 0x80808080u) != 0u) {
+            uint32_t c = 0, pos[4];
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; j++) if (((m >> (8u * j)) & 0xFFu) == 0u) pos[c++] = 4u * q + j;
+            const uint32_t at = atomicAdd(qn, c);
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; j++) if (j < c) Q[at + j] = pos[j];
+        }
+        __syncwarp();
+        uint32_t n = *(volatile uint32_t*)qn;
+        while (n >= 32u) {                                       // warp-uniform
+            n -= 32u;
+            gram_take(S, sp, Q[n + lane], ngram, nnew);
+        }
+        __syncwarp();
+        if (lane == 0) *qn = n;
+        __syncwarp();
     };
     uint32_t q = p0 / 4u + tid;
-    for (; q + 3u * SCAN_THREADS < qe; q += 4u * SCAN_THREADS) {
+    const uint32_t q_warp = q - lane;                            // the loops' conditions are the same for a whole warp
+    uint32_t base = q_warp;
+    for (; base + 3u * SCAN_THREADS + 32u <= qe; base += 4u * SCAN_THREADS, q += 4u * SCAN_THREADS) {
         const uint32_t a0 = __ldg(w + q), a1 = __ldg(w + q + SCAN_THREADS), a2 = __ldg(w + q + 2u * SCAN_THREADS), a3 = __ldg(w + q + 3u * SCAN_THREADS);
-        test(q, a0); test(q + SCAN_THREADS, a1); test(q + 2u * SCAN_THREADS, a2); test(q + 3u * SCAN_THREADS, a3);
+        test(q, a0, true); test(q + SCAN_THREADS, a1, true); test(q + 2u * SCAN_THREADS, a2, true); test(q + 3u * SCAN_THREADS, a3, true);
     }
-    for (; q < qe; q += SCAN_THREADS) test(q, __ldg(w + q));
+    for (; base < qe; base += SCAN_THREADS, q += SCAN_THREADS) {
+        const bool live = q < qe;
+        test(q, live ? __ldg(w + q) : 0u, live);
+    }
+    const uint32_t n = *(volatile uint32_t*)qn;                  // what is left: fewer than 32
+    if (lane < n) gram_take(S, sp, Q[lane], ngram, nnew);
     if (count) { if (ngram) atomicAdd(&S.n_chunk_grams, ngram); if (nnew) atomicAdd(&S.n_chunk_new, nnew); }
 }
 

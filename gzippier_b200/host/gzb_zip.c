@@ -26,6 +26,7 @@
  */
 #define _GNU_SOURCE
 #include "gzb200.h"
+#include "../csrc/gzb_internal.h"
 #include <errno.h>
 #include <fcntl.h>
 #include <pthread.h>
@@ -36,12 +37,11 @@
 #include <time.h>
 #include <unistd.h>
 
-/* not part of the public ABI (gzb_api.cu): waits inside gzb_deflate_host sleep on blocking events instead of spinning */
-void gzb_internal_blocking_sync(gzb_ctx *ctx, int on);
-
 #define MAX_GPUS 16
 #define MAX_WORKERS (2 * MAX_GPUS)
 #define MAX_SLOTS (MAX_WORKERS + 2)
+
+static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec; }
 
 static uint64_t batch_bytes(void)               /* multiple of both chunk sizes */
 {
@@ -241,7 +241,6 @@ static void *writer(void *arg)
     }
 }
 
-static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec; }
 
 /* ---- what outlives a call ---------------------------------------------------------------------------------------
  * Creating a context (CUDA streams, 2 GiB of device scratch) and page-locking the batch slots (~0.3 s per GiB) cost more
@@ -288,11 +287,13 @@ static int pool_contexts(int ng, int wpg)
 /* ---- file to file ------------------------------------------------------------------------------------------------
  * When both ends are regular files nothing has to pass through ONE reader and ONE writer: batch i is the bytes
  * [base + i * BATCH, ...) of the input, its dictionary the 32 KiB in front of them, and its place in the output is known
- * as soon as the sizes of the batches before it are.  So every worker takes the next batch, reads it (dictionary included,
- * one contiguous range) into its own pinned slot, compresses it and writes the fragment at its offset; the copies between
- * page cache and slots are cut into pieces and done by a pool of I/O threads (one per CPU) that all workers share.  The
- * serial reader / in-order writer above remain for pipes, terminals, append-mode output and the member-per-batch mode. */
-#define IO_PIECE ((size_t)2 << 20)
+ * as soon as the sizes of the batches before it are.  So the batches are dealt round-robin to one worker per GPU, and each
+ * worker runs them through its context's own pipeline (gzb_internal_deflate_batches: H2D of batch k+1 || kernels of batch k
+ * || D2H of batch k-1 over the context's pinned staging): the `fetch` callback reads a batch (dictionary included, one
+ * contiguous range) straight into the staging buffer, the `emit` callback writes the fragment at its offset; the copies
+ * between page cache and staging are cut into pieces and done by a pool of I/O threads (one per CPU) that all workers share.
+ * The serial reader / in-order writer above remain for pipes, terminals, append-mode output and the member-per-batch mode. */
+static size_t IO_PIECE = (size_t)2 << 20;      /* GZB_ZIP_IO_PIECE_KB */
 #define IO_QUEUE 8192
 #define IO_MAX_THREADS 128
 typedef struct { int pending, rc; } io_group;
@@ -328,21 +329,27 @@ static void *io_thread(void *arg)
     return NULL;
 }
 
-/* copy [off, off + len) of fd to / from buf on the pool; returns when all of it is done */
-static int io_run(io_pool *io, int fd, int wr, uint8_t *buf, size_t len, off_t off)
+/* queue the copy of [off, off + len) of fd to / from buf in pieces of `piece` bytes; g counts them down */
+static void io_submit(io_pool *io, io_group *g, int fd, int wr, uint8_t *buf, size_t len, off_t off, size_t piece)
 {
-    io_group g = { 0, 0 };
     pthread_mutex_lock(&io->mu);
-    for (size_t o = 0; o < len; o += IO_PIECE) {
+    for (size_t o = 0; o < len; o += piece) {
         while (io->tail - io->head == IO_QUEUE) pthread_cond_wait(&io->done, &io->mu);     /* full: never in practice */
         io_piece *pc = &io->q[io->tail++ % IO_QUEUE];
-        pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->len = len - o < IO_PIECE ? len - o : IO_PIECE; pc->off = off + (off_t)o; pc->grp = &g;
-        g.pending++;
+        pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->len = len - o < piece ? len - o : piece; pc->off = off + (off_t)o; pc->grp = g;
+        g->pending++;
     }
     pthread_cond_broadcast(&io->work);
-    while (g.pending) pthread_cond_wait(&io->done, &io->mu);
     pthread_mutex_unlock(&io->mu);
-    return g.rc;
+}
+/* until every piece of g is done; returns the group's status and clears it */
+static int io_wait(io_pool *io, io_group *g)
+{
+    pthread_mutex_lock(&io->mu);
+    while (g->pending) pthread_cond_wait(&io->done, &io->mu);
+    const int rc = g->rc; g->rc = 0;
+    pthread_mutex_unlock(&io->mu);
+    return rc;
 }
 
 typedef struct {
@@ -351,13 +358,13 @@ typedef struct {
     int ifd, ofd, level, rc; uint32_t flags;
     off_t base, obase;                 /* first input byte; first output byte after the header */
     uint64_t n, batch, dict_sz, out_cap, nb;
-    uint64_t next;                     /* next batch to hand out */
+    int nw;                            /* workers: batch i belongs to worker i % nw */
     uint64_t known;                    /* batches [0, known) have their sizes in; pre[known] is final */
     uint64_t *pre;                     /* pre[i] = bytes of the fragments before batch i  (nb + 1 entries) */
     uint64_t *size; uint32_t *crc; uint8_t *have;
     gzb_ctx *ctx[MAX_WORKERS];
 } direct_t;
-typedef struct { direct_t *d; int w; } direct_arg;
+typedef struct { direct_t *d; int w; io_group rg, wg[2]; double t_fetch, t_wait, t_write, t_all; } direct_arg;   /* t_*: seconds, for GZB_ZIP_VERBOSE */
 
 static void direct_fail(direct_t *d, int rc)
 {
@@ -367,44 +374,70 @@ static void direct_fail(direct_t *d, int rc)
     pthread_mutex_unlock(&d->mu);
 }
 
+static int direct_fetch(void *user, uint64_t k, uint8_t *dst, uint32_t dict_sz, uint64_t *len, int *have_dict, int *final)
+{
+    direct_t *d = ((direct_arg *)user)->d;
+    const uint64_t i = k * (uint64_t)d->nw + (uint64_t)((direct_arg *)user)->w;      /* batches are dealt round-robin to the workers */
+    const uint64_t off = i * d->batch, n = d->n - off < d->batch ? d->n - off : d->batch;
+    const uint64_t dict = i > 0 ? dict_sz : 0;                            /* the bytes in front of the batch are its dictionary */
+    pthread_mutex_lock(&d->mu);
+    const int bad = d->rc != GZB_OK;
+    pthread_mutex_unlock(&d->mu);
+    if (bad) return GZB_E_IO;                                             /* somebody else failed: stop reading */
+    const double t0 = now_s();
+    io_submit(d->io, &((direct_arg *)user)->rg, d->ifd, 0, dst - dict, (size_t)(dict + n), d->base + (off_t)(off - dict), IO_PIECE);
+    if (io_wait(d->io, &((direct_arg *)user)->rg)) return GZB_E_IO;
+    ((direct_arg *)user)->t_fetch += now_s() - t0;
+    *len = n; *have_dict = dict != 0; *final = i + 1 == d->nb;
+    return GZB_OK;
+}
+
+static int direct_emit(void *user, uint64_t k, const uint8_t *src, const gzb_result *r)
+{
+    direct_t *d = ((direct_arg *)user)->d;
+    const uint64_t i = k * (uint64_t)d->nw + (uint64_t)((direct_arg *)user)->w;
+    const double t0 = now_s();
+    pthread_mutex_lock(&d->mu);
+    d->size[i] = r->out_bytes; d->crc[i] = r->crc32; d->have[i] = 1;
+    while (d->known < d->nb && d->have[d->known]) { d->pre[d->known + 1] = d->pre[d->known] + d->size[d->known]; d->known++; }
+    pthread_cond_broadcast(&d->cv);
+    /* every worker takes its batches in rising order and announces a size before it waits: the oldest batch never waits */
+    while (d->rc == GZB_OK && d->known < i) pthread_cond_wait(&d->cv, &d->mu);
+    const int bad = d->rc != GZB_OK;
+    const uint64_t at = d->pre[i];
+    pthread_mutex_unlock(&d->mu);
+    if (bad) return GZB_E_IO;
+    /* Writes to one file do not run side by side -- the kernel takes the inode's lock for each (3.8 GB/s into a fresh tmpfs
+     * file on the B200 hosts however many threads write, tools/micro_pwrite.c) -- so the fragment goes as few large pieces,
+     * and the worker does not wait for them: direct_emit_done does, two batches later. */
+    io_submit(d->io, &((direct_arg *)user)->wg[k & 1], d->ofd, 1, (uint8_t *)(uintptr_t)src, (size_t)r->out_bytes, d->obase + (off_t)at, (size_t)16 << 20);
+    ((direct_arg *)user)->t_wait += now_s() - t0;
+    return GZB_OK;
+}
+
+static int direct_emit_done(void *user, uint64_t k)
+{
+    direct_arg *a = (direct_arg *)user;
+    const double t0 = now_s();
+    const int rc = io_wait(a->d->io, &a->wg[k & 1]) ? GZB_E_IO : GZB_OK;
+    a->t_write += now_s() - t0;
+    return rc;
+}
+
 static void *direct_worker(void *arg)
 {
-    direct_t *d = ((direct_arg *)arg)->d;
-    const int w = ((direct_arg *)arg)->w;
-    uint8_t *in = g_pool.in[w], *out = g_pool.out[w];                    /* slot w is this worker's */
-    if (!in) {                                                            /* page-locked on first use, kept by the pool */
-        int rc = gzb_host_alloc(d->ctx[w], GZB_DICT + d->batch, (void **)&in);
-        g_pool.in[w] = in;
-        if (rc == GZB_OK) { rc = gzb_host_alloc(d->ctx[w], d->out_cap, (void **)&out); g_pool.out[w] = out; }
-        if (rc != GZB_OK) { direct_fail(d, rc); return NULL; }
-    }
-    for (;;) {
-        pthread_mutex_lock(&d->mu);
-        const uint64_t i = d->next;
-        const int stop = d->rc != GZB_OK || i >= d->nb;
-        if (!stop) d->next = i + 1;
-        pthread_mutex_unlock(&d->mu);
-        if (stop) return NULL;
-        const uint64_t off = i * d->batch, len = d->n - off < d->batch ? d->n - off : d->batch;
-        const uint64_t dict = i > 0 ? d->dict_sz : 0;                     /* the bytes in front of the batch are its dictionary */
-        uint8_t *data = in + GZB_DICT;
-        if (io_run(d->io, d->ifd, 0, data - dict, (size_t)(dict + len), d->base + (off_t)(off - dict))) { direct_fail(d, GZB_E_IO); return NULL; }
-        gzb_result res;
-        int rc = gzb_deflate_host(d->ctx[w], d->level, d->flags | (i + 1 == d->nb ? GZB_F_FINAL : 0u), data, len,
-                                  dict ? data - dict : NULL, out, d->out_cap, &res);
-        if (rc != GZB_OK) { direct_fail(d, rc); return NULL; }
-        pthread_mutex_lock(&d->mu);
-        d->size[i] = res.out_bytes; d->crc[i] = res.crc32; d->have[i] = 1;
-        while (d->known < d->nb && d->have[d->known]) { d->pre[d->known + 1] = d->pre[d->known] + d->size[d->known]; d->known++; }
-        pthread_cond_broadcast(&d->cv);
-        /* batches are handed out in order and a worker publishes its size before it waits: the oldest one never waits */
-        while (d->rc == GZB_OK && d->known < i) pthread_cond_wait(&d->cv, &d->mu);
-        const int bad = d->rc != GZB_OK;
-        const uint64_t at = d->pre[i];
-        pthread_mutex_unlock(&d->mu);
-        if (bad) return NULL;
-        if (io_run(d->io, d->ofd, 1, out, (size_t)res.out_bytes, d->obase + (off_t)at)) { direct_fail(d, GZB_E_IO); return NULL; }
-    }
+    direct_arg *a = (direct_arg *)arg;
+    direct_t *d = a->d;
+    gzb_batch_io io;
+    memset(&io, 0, sizeof(io));
+    io.user = a; io.max_bytes = d->batch; io.blocking = 1;               /* waiting workers leave their CPUs to the I/O threads */
+    io.n_batches = d->nb > (uint64_t)a->w ? (d->nb - (uint64_t)a->w + (uint64_t)d->nw - 1) / (uint64_t)d->nw : 0;
+    io.fetch = direct_fetch; io.emit = direct_emit; io.emit_done = direct_emit_done;
+    const double t0 = now_s();
+    const int rc = gzb_internal_deflate_batches(d->ctx[a->w], d->level, d->flags, &io);
+    a->t_all = now_s() - t0;
+    if (rc != GZB_OK) direct_fail(d, rc);
+    return NULL;
 }
 
 /* the body of a member, file to file: n input bytes at base -> fragments from obase on.  The pool's lock is held. */
@@ -417,6 +450,7 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
     d->ifd = ifd; d->ofd = ofd; d->level = o->level; d->flags = flags; d->base = base; d->obase = obase; d->n = n;
     d->batch = batch; d->out_cap = out_cap; d->dict_sz = (flags & GZB_F_RSYNCABLE) ? 0 : GZB_DICT;
     d->nb = (n + batch - 1) / batch; d->rc = GZB_OK; d->io = &io;
+    d->nw = nw;
     for (int w = 0; w < nw; w++) d->ctx[w] = g_pool.ctx[w];
     d->pre = (uint64_t *)calloc(d->nb + 1, sizeof(uint64_t)); d->size = (uint64_t *)calloc(d->nb, sizeof(uint64_t));
     d->crc = (uint32_t *)calloc(d->nb, sizeof(uint32_t)); d->have = (uint8_t *)calloc(d->nb, 1);
@@ -426,6 +460,7 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     int want = ncpu > 0 ? (int)ncpu : 8;
     { const char *e = getenv("GZB_ZIP_IO_THREADS"); if (e && atoi(e) > 0) want = atoi(e); }
+    { const char *e = getenv("GZB_ZIP_IO_PIECE_KB"); IO_PIECE = (size_t)(e && atoi(e) >= 64 ? atoi(e) : 2048) << 10; }
     if (want > IO_MAX_THREADS) want = IO_MAX_THREADS;
     pthread_t th[MAX_WORKERS]; direct_arg wa[MAX_WORKERS]; int nth = 0;
     if (rc == GZB_OK) {
@@ -434,12 +469,16 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
     }
     if (rc == GZB_OK) {
         for (int w = 0; w < nw; w++) {
-            wa[w].d = d; wa[w].w = w;
+            memset(&wa[w], 0, sizeof(wa[w])); wa[w].d = d; wa[w].w = w;
             if (pthread_create(&th[w], NULL, direct_worker, &wa[w])) { direct_fail(d, GZB_E_NOMEM); break; }
             nth++;
         }
         for (int w = 0; w < nth; w++) pthread_join(th[w], NULL);
         rc = d->rc;
+        if (getenv("GZB_ZIP_VERBOSE"))
+            for (int w = 0; w < nth; w++)
+                fprintf(stderr, "gzb_zip_fd: worker %d: %.3f s in all, of which reading %.3f s, waiting for its offset %.3f s, waiting for its writes %.3f s (%d I/O threads)\n",
+                        w, wa[w].t_all, wa[w].t_fetch, wa[w].t_wait, wa[w].t_write, io.nth);
     }
     pthread_mutex_lock(&io.mu); io.stop = 1; pthread_cond_broadcast(&io.work); pthread_mutex_unlock(&io.mu);
     for (int k = 0; k < io.nth; k++) pthread_join(io.th[k], NULL);
@@ -525,19 +564,16 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
 
     /* file to file, and more than a small input: no serial stage at all (zip_direct) */
     if (regular && p->out_regular && !o->members && in_left > SMALL && !getenv("GZB_ZIP_NO_DIRECT")) {
-        /* a worker reads, compresses and writes one batch after the other: four of them per GPU keep its kernels back to back */
-        int wpg = 4;
+        /* one worker (thread + context) per GPU: its batches overlap inside gzb_internal_deflate_batches */
+        int wpg = 1;
         { const char *e = getenv("GZB_ZIP_WORKERS_PER_GPU"); if (e && atoi(e) > 0) wpg = atoi(e); }
         if (wpg * ng > MAX_WORKERS) wpg = MAX_WORKERS / ng;
         { const uint64_t nb = (in_left + p->batch - 1) / p->batch; while (wpg > 1 && (uint64_t)(wpg - 1) * (uint64_t)ng >= nb) wpg--; }
         const int nw = wpg * ng;
         if ((rc = pool_contexts(ng, wpg)) != GZB_OK) goto done;
-        if (g_pool.batch != p->batch || g_pool.out_cap != p->out_cap) { pool_free_slots(); g_pool.batch = p->batch; g_pool.out_cap = p->out_cap; }
-        for (int w = 0; w < nw; w++) gzb_internal_blocking_sync(g_pool.ctx[w], 1);             /* waiting workers leave their CPUs to the I/O threads */
         t_setup = now_s();
         uint32_t crc = 0; uint64_t ob = 0; uint8_t tr[8];
         rc = zip_direct(ifd, ofd, o, p->flags, nw, pos, in_left, p->opos, p->batch, p->out_cap, &crc, &ob);
-        for (int w = 0; w < nw; w++) gzb_internal_blocking_sync(g_pool.ctx[w], 0);
         if (rc == GZB_OK) {
             pos += (off_t)in_left; p->opos += (off_t)ob; o->bytes_in = in_left; o->bytes_out += ob;
             gzb_gzip_trailer(crc, in_left, tr, sizeof(tr));
