@@ -106,7 +106,12 @@ def have_ref():
 
 def ref_gzip(data, level=6, threads=0, rsyncable=False):
     cmd = [REFGZIP, f"-{level}"] + (["-j", str(threads)] if threads else []) + (["--rsyncable"] if rsyncable else [])
-    return subprocess.run(cmd, input=bytes(_arr(data).tobytes()), stdout=subprocess.PIPE, check=True, timeout=600).stdout
+    # from a regular file, not a pipe: the reference's single-stream loop takes any short read for the end of the input
+    # (src/zip.c:76-92: flush = avail_in != CHUNK ? Z_FINISH : ...), so a pipe whose writer is a moment late truncates it
+    import tempfile
+    with tempfile.TemporaryFile() as f:
+        f.write(_arr(data).tobytes()); f.flush(); f.seek(0)
+        return subprocess.run(cmd, stdin=f, stdout=subprocess.PIPE, check=True, timeout=600).stdout
 
 
 def ref_gunzip(member):

@@ -461,15 +461,23 @@ def test_device_side_verify(gz, orc, ctx):
 
 
 def test_more_than_4_gib_in_one_call(gz, ctx):
-    """64-bit offsets everywhere and ISIZE mod 2^32 (src/parallel.c:60,545): 4 GiB + 3 chunks + 11 bytes in one device call,
-    checked by the device-side round trip, the CRC and a zlib decode of the last fragments."""
+    """64-bit offsets everywhere and ISIZE mod 2^32 (src/parallel.c:60,545): 4 GiB + 3 chunks + 11 bytes in one device call at
+    -6, checked over its whole length twice: by the device-side round trip (k_verify) and by zlib, which decodes the complete
+    body -- the chunks on either side of the 4 GiB line included -- and must give back every input byte."""
     import torch
     n = (4 << 30) + 3 * gz.CHUNK + 11
     d = gz.corpus("text", n, seed=13)
     t = torch.from_numpy(d).cuda()
     out = torch.empty(gz.bound(n), dtype=torch.uint8, device="cuda")
-    r = ctx.deflate_device(t, n, out, 1, flags=gz.F_FINAL | gz.F_VERIFY)
+    r = ctx.deflate_device(t, n, out, 6, flags=gz.F_FINAL | gz.F_VERIFY)
     assert r.in_bytes == n and r.crc32 == zlib.crc32(memoryview(d))
     assert gz.gzip_trailer(r.crc32, r.in_bytes)[4:] == (n % (1 << 32)).to_bytes(4, "little")
-    raw = out[: r.out_bytes].cpu().numpy().tobytes()
-    assert zlib.decompress(raw, -15, ) [-1000:] == d[-1000:].tobytes()
+    raw = out[: r.out_bytes].cpu().numpy()
+    del t, out
+    z, pos, step = zlib.decompressobj(-15), 0, 32 << 20
+    for off in range(0, raw.size, step):
+        back = z.decompress(memoryview(raw[off:off + step]))
+        assert back == d[pos:pos + len(back)].tobytes(), f"decoded bytes differ somewhere in [{pos}, {pos + len(back)})"
+        pos += len(back)
+    back = z.flush()
+    assert back == d[pos:pos + len(back)].tobytes() and pos + len(back) == n and z.eof

@@ -66,6 +66,9 @@ def test_header_trailer_known_answers(orc, golden):
             assert orc.gzip_trailer(e["crc32"], e["n"]).hex() == v["tail"]
         for level, v in e["single"].items():
             assert orc.gzip_header_single(int(level)).hex() == v["head"]
+            # the whole input is in the member (the reference's single-stream loop ends at a short read, src/zip.c:76-92: a
+            # golden made through a pipe can be a truncated one -- three of round 1's were)
+            assert orc.gzip_trailer(e["crc32"], e["n"]).hex() == v["tail"], (kind, level)
     assert orc.gzip_header(6, 0x01020304, b"dir/file.txt") == bytes([31, 139, 8, 8, 4, 3, 2, 1, 0, 3]) + b"dir/file.txt\0"
 
 
