@@ -73,6 +73,46 @@ def test_degenerate_inputs(gz, orc, ctx):
             assert raw.tobytes() == orc.engine_model(d, level).tobytes()
 
 
+def _lz_structured(rng, n, max_dist, lit_run=12):
+    """bytes built the way an LZ77 decoder builds them: short literal runs and copies at chosen distances and lengths"""
+    out = bytearray(rng.integers(0, 256, 64, dtype=np.uint8).tobytes())
+    while len(out) < n:
+        if rng.random() < 0.35:
+            out += rng.integers(97, 123, int(rng.integers(1, lit_run)), dtype=np.uint8).tobytes()
+        else:
+            dist = int(min(len(out), rng.choice([1, 2, 3, 4, 5, 6, 7, 255, 256, 257, 258, 259, 4096, 32766, 32767, 32768, int(rng.integers(1, max_dist))])))
+            ln = int(rng.choice([3, 4, 5, 6, 7, 8, 16, 17, 257, 258, 259, 300, int(rng.integers(3, 600))]))
+            for _ in range(ln):
+                out.append(out[-dist])
+    return np.frombuffer(bytes(out[:n]), dtype=np.uint8).copy()
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_structured_inputs_equal_the_model(gz, orc, ctx, seed):
+    """Inputs aimed at the edges of the match finder: periods around the longest match (258) and the window (32 KiB),
+    copies that straddle tile (2 KiB), block (64 KiB) and chunk (128 KiB) boundaries, distances of exactly 32768 and one
+    beyond, and chunks of random bytes between compressible ones (k_lz77's segments).  Bytes must equal the sequential
+    model and decode with zlib."""
+    rng = np.random.default_rng(1000 + seed)
+    cases = []
+    for period in (1, 2, 3, 5, 6, 7, 257, 258, 259, 2047, 2048, 2049, 32767, 32768, 32769, 65536)[seed::6]:
+        unit = rng.integers(0, 256, period, dtype=np.uint8)
+        cases.append((f"period {period}", np.tile(unit, (3 * gz.CHUNK + 4097) // period + 1)[: 3 * gz.CHUNK + 4097]))
+    cases.append(("lz near", _lz_structured(rng, 2 * gz.CHUNK + int(rng.integers(1, 5000)), 300)))
+    cases.append(("lz far", _lz_structured(rng, 3 * gz.CHUNK + int(rng.integers(1, 5000)), 40000)))
+    parts = []                                                   # text / random / text / random ... in chunk-sized and ragged pieces
+    for k in range(7):
+        ln = gz.CHUNK if k % 3 else int(rng.integers(1000, 2 * gz.CHUNK))
+        parts.append(rng.integers(0, 256, ln, dtype=np.uint8) if (k + seed) % 2 else gz.corpus("text", ln, seed=seed * 16 + k))
+    cases.append(("segments", np.concatenate(parts)))
+    for name, d in cases:
+        for level in (1, 5, 9):
+            raw, r = ctx.deflate_host(d, level)
+            assert r.crc32 == zlib.crc32(d.tobytes())
+            assert raw.tobytes() == orc.engine_model(d, level).tobytes(), (name, level, d.size)
+            assert zlib.decompress(raw.tobytes(), -15) == d.tobytes(), (name, level)
+
+
 def test_rsyncable(gz, orc, ctx, golden):
     e = golden["corpora"]["text"]
     d = gz.corpus("text", e["n"], seed=golden["seed"])
@@ -311,7 +351,7 @@ def test_kernel_variants_give_the_same_bytes(gz, orc, monkeypatch, pw, help_):
             ctx.close()
 
 
-@pytest.mark.parametrize("layout", ["0", "1", "2"])
+@pytest.mark.parametrize("layout", ["0", "1", "2", "3"])
 def test_warp_role_layouts_give_the_same_bytes(gz, orc, monkeypatch, layout):
     """What each warp of a k_lz77 CTA does (inserters, parsers, search; which scheduler they sit on) is a launch parameter
     (lz77_role_map, GZB_ROLEMAP); scheduling only, never a byte."""
