@@ -492,10 +492,13 @@ def main():
         # k_lz77 carries the step's 1 B read + 1/ratio B written per input byte; k_scan reads every byte once
         alg_bytes = (n if scan_bound else n + res["out_bytes"]) / nsub
         achieved = alg_bytes / (top_ms / 1e3) / 1e9
-        traffic = None
+        traffic, issue = None, None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "lz77_traffic.json")))
             traffic = prof["k_scan_dram_bytes_per_input_byte" if scan_bound else "dram_bytes_per_input_byte"] * n / nsub
+            if not scan_bound:      # what actually bounds k_lz77 (from the committed ncu capture, not measured in this run)
+                issue = {"issue_slots_busy_pct": prof["issue_active_pct"], "warp_inst_per_input_byte": round(prof["warp_inst_per_input_byte"], 2),
+                         "source": prof["capture"] + " (text at -6)"}
         except (OSError, KeyError, ValueError):
             pass
         ms, steps = res["ms"], a.steps
@@ -512,6 +515,8 @@ def main():
                              "note": ("stored chunks: the scan (CRC-32 + byte histogram + gram probe) is the step; traffic is the text capture's" if scan_bound else
                                       "integer/latency-bound path: the HBM fraction is small by construction (SURVEY 8d); see profiles/ for issue-slot utilisation")},
                 "cpu_baseline": cpu, "clocks": res["clocks"]}
+        if issue:
+            line["roofline"]["issue"] = issue
         if e2e_fd:
             line["e2e_fd"] = e2e_fd
         if member:
