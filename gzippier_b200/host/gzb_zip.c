@@ -300,7 +300,12 @@ typedef struct { int pending, rc; } io_group;
 typedef struct { int fd, wr; uint8_t *buf; size_t len; off_t off; io_group *grp; } io_piece;
 typedef struct {
     pthread_mutex_t mu; pthread_cond_t work, done;
-    io_piece q[IO_QUEUE]; unsigned head, tail;      /* head: next to take, tail: next free */
+    /* two rings, [0] reads and [1] writes (head: next to take, tail: next free).  Reads run on as many threads as there
+     * are; writes into the one output file exclude each other in the kernel (the inode's lock), so at most max_writers
+     * threads (1) are in a write at a time -- more of them only queue on that lock and slow each other down (measured on
+     * 2 GPUs, 24 CPUs, 16 GiB text: 16.3 GB/s with one writer at a time, 13.7 with two, 13.9 with four). */
+    io_piece q[2][IO_QUEUE]; unsigned head[2], tail[2];
+    int writers, max_writers;
     int stop, nth; pthread_t th[IO_MAX_THREADS];
 } io_pool;
 
@@ -309,9 +314,16 @@ static void *io_thread(void *arg)
     io_pool *io = (io_pool *)arg;
     pthread_mutex_lock(&io->mu);
     for (;;) {
-        while (io->head == io->tail && !io->stop) pthread_cond_wait(&io->work, &io->mu);
-        if (io->head == io->tail) break;
-        io_piece pc = io->q[io->head++ % IO_QUEUE];
+        int k;
+        for (;;) {
+            if (io->head[1] != io->tail[1] && io->writers < io->max_writers) { k = 1; break; }
+            if (io->head[0] != io->tail[0]) { k = 0; break; }
+            if (io->stop && io->head[1] == io->tail[1]) { k = -1; break; }
+            pthread_cond_wait(&io->work, &io->mu);
+        }
+        if (k < 0) break;
+        io_piece pc = io->q[k][io->head[k]++ % IO_QUEUE];
+        io->writers += k;
         pthread_mutex_unlock(&io->mu);
         int rc = 0; size_t done = 0;
         while (done < pc.len) {
@@ -323,6 +335,7 @@ static void *io_thread(void *arg)
         }
         pthread_mutex_lock(&io->mu);
         if (rc) pc.grp->rc = rc;
+        if (k) { io->writers--; if (io->head[1] != io->tail[1]) pthread_cond_signal(&io->work); }   /* a waiting write may go now */
         if (--pc.grp->pending == 0) pthread_cond_broadcast(&io->done);
     }
     pthread_mutex_unlock(&io->mu);
@@ -334,8 +347,9 @@ static void io_submit(io_pool *io, io_group *g, int fd, int wr, uint8_t *buf, si
 {
     pthread_mutex_lock(&io->mu);
     for (size_t o = 0; o < len; o += piece) {
-        while (io->tail - io->head == IO_QUEUE) pthread_cond_wait(&io->done, &io->mu);     /* full: never in practice */
-        io_piece *pc = &io->q[io->tail++ % IO_QUEUE];
+        const int k = wr ? 1 : 0;
+        while (io->tail[k] - io->head[k] == IO_QUEUE) pthread_cond_wait(&io->done, &io->mu);     /* full: never in practice */
+        io_piece *pc = &io->q[k][io->tail[k]++ % IO_QUEUE];
         pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->len = len - o < piece ? len - o : piece; pc->off = off + (off_t)o; pc->grp = g;
         g->pending++;
     }
@@ -460,6 +474,8 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     int want = ncpu > 0 ? (int)ncpu : 8;
     { const char *e = getenv("GZB_ZIP_IO_THREADS"); if (e && atoi(e) > 0) want = atoi(e); }
+    io.max_writers = 1;
+    { const char *e = getenv("GZB_ZIP_WRITERS"); if (e && atoi(e) > 0) io.max_writers = atoi(e); }
     { const char *e = getenv("GZB_ZIP_IO_PIECE_KB"); IO_PIECE = (size_t)(e && atoi(e) >= 64 ? atoi(e) : 2048) << 10; }
     if (want > IO_MAX_THREADS) want = IO_MAX_THREADS;
     pthread_t th[MAX_WORKERS]; direct_arg wa[MAX_WORKERS]; int nth = 0;
