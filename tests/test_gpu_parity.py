@@ -422,6 +422,43 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
         assert e.value.code == gz.E_IO
 
 
+def test_zip_fd_file_to_file_variants(gz, orc, ctx, tmp_path, monkeypatch):
+    """The file-to-file path of gzb_zip_fd away from its defaults: --rsyncable (16 KiB chunks, no dictionary between
+    batches), FNAME / MTIME in the header, an input descriptor that does not stand at the start of its file, more workers
+    than batches, several workers per GPU, a single I/O thread.  Always: header + the one-shot body + trailer."""
+    n = (41 << 20) + 4321
+    d = gz.corpus("mixed", n, seed=77)
+    src = tmp_path / "in.bin"; src.write_bytes(b"skip me" * 1000 + d.tobytes())
+    skip = 7000
+    def run(**kw):
+        dst = tmp_path / "o.gz"
+        with open(src, "rb") as fi, open(dst, "wb") as fo:
+            fi.seek(skip)
+            bi, bo = gz.zip_fd(fi.fileno(), fo.fileno(), **kw)
+            assert fi.tell() == skip + n
+        m = dst.read_bytes()
+        assert bi == n and bo == len(m)
+        return m
+    crc = zlib.crc32(d.tobytes())
+    monkeypatch.setenv("GZB_ZIP_BATCH_MB", "4")
+    body6 = orc.engine_model(d, 6).tobytes()
+    m = run(level=6, name=b"in.bin", mtime=0x01020304)
+    assert m[:10] == bytes([31, 139, 8, 8, 4, 3, 2, 1, 0, 3]) and m[10:17] == b"in.bin\0"
+    assert m[17:-8] == body6 and m[-8:] == gz.gzip_trailer(crc, n)
+    for env in ({"GZB_ZIP_WORKERS_PER_GPU": "3"}, {"GZB_ZIP_IO_THREADS": "1"}, {"GZB_ZIP_BATCH_MB": "64"}, {"GZB_ZIP_WRITERS": "3", "GZB_ZIP_IO_PIECE_KB": "64"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        m = run(level=6)
+        assert m[10:-8] == body6 and m[-8:] == gz.gzip_trailer(crc, n), env
+        for k in env:
+            monkeypatch.delenv(k)
+        monkeypatch.setenv("GZB_ZIP_BATCH_MB", "4")
+    raw, r = ctx.deflate_host(d, 6, gz.F_FINAL | gz.F_RSYNCABLE)
+    m = run(level=6, rsyncable=True)
+    assert m[10:-8] == raw.tobytes() and zlib.decompress(m, 31) == d.tobytes()
+    gz.zip_release()
+
+
 def test_zip_fd_member_per_batch(gz, orc, tmp_path, monkeypatch):
     """opts.members (BASELINE config 5's "per-GPU members concatenated"): every batch a complete member.
     Multi-member decoders restore the whole input; each member is what a one-shot call on that batch gives; and the
