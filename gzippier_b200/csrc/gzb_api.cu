@@ -787,9 +787,10 @@ int gzb_internal_deflate_batches(gzb_ctx* ctx, int level, uint32_t flags, const 
             r = enqueue_deflate(ctx, level, f, ctx->d_in[sl] + dsz, S.len, halo, ctx->d_out[sl], ctx->dev_out_cap, ctx->stream);
             if (r != GZB_OK) return r;
             CU(ctx, cudaEventRecord(ctx->e_cmp[sl], ctx->stream));
-            // ... and under them the host passes on batch k-1 (its D2H was the last thing of the round before) and reads batch k+1
-            if ((r = emit_slot(sl ^ 1)) != GZB_OK) return r;
+            // ... and under them the host reads batch k+1 -- first, because read + H2D of a batch together take about as long as
+            // the kernels of one, and the next kernels can only start when they are through -- and passes on batch k-1
             if (k + 1 < io->n_batches && (r = fetch_h2d(k + 1)) != GZB_OK) return r;
+            if ((r = emit_slot(sl ^ 1)) != GZB_OK) return r;
             CU(ctx, wait_event(ctx->e_cmp[sl], ctx->e_blk_cmp, ctx->stream));   // out_bytes of batch k is known now
             if ((r = release_slot(sl)) != GZB_OK) return r;                  // batch k-2 has left the pinned slot
             const Cursor c = *ctx->h_cursor;

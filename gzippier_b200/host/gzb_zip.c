@@ -14,8 +14,9 @@
  *   writer   (one thread)       header, fragments in batch order, CRCs folded with
  *                               crc32_combine (:544), trailer (:496-507, :538, :555-556)
  *
- * Between two regular files none of this is serial (zip_direct below): every worker reads its own batches and writes its
- * fragments at their final offsets, the copies spread over one I/O thread per CPU.
+ * Between two regular files none of this is serial (zip_direct below): every worker reads its own batches and places its
+ * fragments at their final offsets (reserved with fallocate, filled through a shared mapping), the copies spread over one
+ * I/O thread per CPU.
  *
  * Batches are independent given their dictionary, so with n_gpus > 1 consecutive batches simply
  * go to different GPUs: contiguous shards on chunk boundaries, no collective.
@@ -33,6 +34,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <stdio.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <time.h>
 #include <unistd.h>
@@ -297,7 +299,8 @@ static size_t IO_PIECE = (size_t)2 << 20;      /* GZB_ZIP_IO_PIECE_KB */
 #define IO_QUEUE 8192
 #define IO_MAX_THREADS 128
 typedef struct { int pending, rc; } io_group;
-typedef struct { int fd, wr; uint8_t *buf; size_t len; off_t off; io_group *grp; } io_piece;
+enum { IO_READ = 0, IO_WRITE = 1, IO_COPY = 2 };     /* pread into buf; pwrite from buf; memcpy(dst, buf) */
+typedef struct { int fd, wr; uint8_t *buf, *dst; size_t len; off_t off; io_group *grp; } io_piece;
 typedef struct {
     pthread_mutex_t mu; pthread_cond_t work, done;
     /* two rings, [0] reads and [1] writes (head: next to take, tail: next free).  Reads run on as many threads as there
@@ -326,6 +329,7 @@ static void *io_thread(void *arg)
         io->writers += k;
         pthread_mutex_unlock(&io->mu);
         int rc = 0; size_t done = 0;
+        if (pc.wr == IO_COPY) { memcpy(pc.dst, pc.buf, pc.len); done = pc.len; }
         while (done < pc.len) {
             ssize_t r = pc.wr ? pwrite(pc.fd, pc.buf + done, pc.len - done, pc.off + (off_t)done)
                               : pread(pc.fd, pc.buf + done, pc.len - done, pc.off + (off_t)done);
@@ -343,14 +347,14 @@ static void *io_thread(void *arg)
 }
 
 /* queue the copy of [off, off + len) of fd to / from buf in pieces of `piece` bytes; g counts them down */
-static void io_submit(io_pool *io, io_group *g, int fd, int wr, uint8_t *buf, size_t len, off_t off, size_t piece)
+static void io_submit(io_pool *io, io_group *g, int fd, int wr, uint8_t *buf, size_t len, off_t off, size_t piece, uint8_t *dst)
 {
     pthread_mutex_lock(&io->mu);
     for (size_t o = 0; o < len; o += piece) {
-        const int k = wr ? 1 : 0;
+        const int k = wr == IO_WRITE ? 1 : 0;
         while (io->tail[k] - io->head[k] == IO_QUEUE) pthread_cond_wait(&io->done, &io->mu);     /* full: never in practice */
         io_piece *pc = &io->q[k][io->tail[k]++ % IO_QUEUE];
-        pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->len = len - o < piece ? len - o : piece; pc->off = off + (off_t)o; pc->grp = g;
+        pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->dst = dst ? dst + o : NULL; pc->len = len - o < piece ? len - o : piece; pc->off = off + (off_t)o; pc->grp = g;
         g->pending++;
     }
     pthread_cond_broadcast(&io->work);
@@ -373,12 +377,13 @@ typedef struct {
     off_t base, obase;                 /* first input byte; first output byte after the header */
     uint64_t n, batch, dict_sz, out_cap, nb;
     int nw;                            /* workers: batch i belongs to worker i % nw */
+    int mfd, map_off; long pagesz;     /* output reopened read-write for the shared mappings (-1: pwrite only); set when fallocate is not supported */
     uint64_t known;                    /* batches [0, known) have their sizes in; pre[known] is final */
     uint64_t *pre;                     /* pre[i] = bytes of the fragments before batch i  (nb + 1 entries) */
     uint64_t *size; uint32_t *crc; uint8_t *have;
     gzb_ctx *ctx[MAX_WORKERS];
 } direct_t;
-typedef struct { direct_t *d; int w; io_group rg, wg[2]; double t_fetch, t_wait, t_write, t_all; } direct_arg;   /* t_*: seconds, for GZB_ZIP_VERBOSE */
+typedef struct { direct_t *d; int w; io_group rg, wg[2]; void *map[2]; size_t maplen[2]; double t_fetch, t_wait, t_write, t_all; } direct_arg;   /* t_*: seconds, for GZB_ZIP_VERBOSE */
 
 static void direct_fail(direct_t *d, int rc)
 {
@@ -399,7 +404,7 @@ static int direct_fetch(void *user, uint64_t k, uint8_t *dst, uint32_t dict_sz, 
     pthread_mutex_unlock(&d->mu);
     if (bad) return GZB_E_IO;                                             /* somebody else failed: stop reading */
     const double t0 = now_s();
-    io_submit(d->io, &((direct_arg *)user)->rg, d->ifd, 0, dst - dict, (size_t)(dict + n), d->base + (off_t)(off - dict), IO_PIECE);
+    io_submit(d->io, &((direct_arg *)user)->rg, d->ifd, IO_READ, dst - dict, (size_t)(dict + n), d->base + (off_t)(off - dict), IO_PIECE, NULL);
     if (io_wait(d->io, &((direct_arg *)user)->rg)) return GZB_E_IO;
     ((direct_arg *)user)->t_fetch += now_s() - t0;
     *len = n; *have_dict = dict != 0; *final = i + 1 == d->nb;
@@ -424,8 +429,32 @@ static int direct_emit(void *user, uint64_t k, const uint8_t *src, const gzb_res
     /* Writes to one file do not run side by side -- the kernel takes the inode's lock for each (3.8 GB/s into a fresh tmpfs
      * file on the B200 hosts however many threads write, tools/micro_pwrite.c) -- so the fragment goes as few large pieces,
      * and the worker does not wait for them: direct_emit_done does, two batches later. */
-    io_submit(d->io, &((direct_arg *)user)->wg[k & 1], d->ofd, 1, (uint8_t *)(uintptr_t)src, (size_t)r->out_bytes, d->obase + (off_t)at, (size_t)16 << 20);
-    ((direct_arg *)user)->t_wait += now_s() - t0;
+    direct_arg *a = (direct_arg *)user;
+    const off_t lo = d->obase + (off_t)at;
+    const size_t len = (size_t)r->out_bytes;
+    a->map[k & 1] = NULL;
+    if (d->mfd >= 0 && len) {
+        /* Reserve, then fill: fallocate() gives the fragment's range its pages (the one serial step, ~15 GB/s; a full file
+         * system is an error code HERE, never a SIGBUS later), then the bytes go into a shared mapping of that range from
+         * all I/O threads at once -- page-table work instead of the inode's lock (tools/micro_fallocwrite.c: 7 GB/s
+         * against 3.8 GB/s for pwrite on the B200 hosts). */
+        if (fallocate(d->mfd, 0, lo, (off_t)len) != 0) {
+            if (errno == EOPNOTSUPP || errno == ENOSYS || errno == EINVAL) { pthread_mutex_lock(&d->mu); d->map_off = 1; pthread_mutex_unlock(&d->mu); }
+            else return GZB_E_IO;
+        } else if (!d->map_off) {
+            const off_t pg = lo & ~(off_t)(d->pagesz - 1);
+            const size_t mlen = (size_t)(lo - pg) + len;
+            void *m = mmap(NULL, mlen, PROT_READ | PROT_WRITE, MAP_SHARED, d->mfd, pg);
+            if (m != MAP_FAILED) {
+                a->map[k & 1] = m; a->maplen[k & 1] = mlen;
+                io_submit(d->io, &a->wg[k & 1], -1, IO_COPY, (uint8_t *)(uintptr_t)src, len, 0, IO_PIECE, (uint8_t *)m + (lo - pg));
+                a->t_wait += now_s() - t0;
+                return GZB_OK;
+            }
+        }
+    }
+    io_submit(d->io, &a->wg[k & 1], d->ofd, IO_WRITE, (uint8_t *)(uintptr_t)src, len, lo, (size_t)16 << 20, NULL);
+    a->t_wait += now_s() - t0;
     return GZB_OK;
 }
 
@@ -434,6 +463,7 @@ static int direct_emit_done(void *user, uint64_t k)
     direct_arg *a = (direct_arg *)user;
     const double t0 = now_s();
     const int rc = io_wait(a->d->io, &a->wg[k & 1]) ? GZB_E_IO : GZB_OK;
+    if (a->map[k & 1]) { munmap(a->map[k & 1], a->maplen[k & 1]); a->map[k & 1] = NULL; }
     a->t_write += now_s() - t0;
     return rc;
 }
@@ -465,6 +495,12 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
     d->batch = batch; d->out_cap = out_cap; d->dict_sz = (flags & GZB_F_RSYNCABLE) ? 0 : GZB_DICT;
     d->nb = (n + batch - 1) / batch; d->rc = GZB_OK; d->io = &io;
     d->nw = nw;
+    d->mfd = -1; d->pagesz = sysconf(_SC_PAGESIZE);
+    if (!getenv("GZB_ZIP_NO_MMAP") && d->pagesz > 0) {                    /* the caller's descriptor is usually write-only: a mapping needs read-write */
+        char path[64];
+        snprintf(path, sizeof(path), "/proc/self/fd/%d", ofd);
+        d->mfd = open(path, O_RDWR | O_CLOEXEC);
+    }
     for (int w = 0; w < nw; w++) d->ctx[w] = g_pool.ctx[w];
     d->pre = (uint64_t *)calloc(d->nb + 1, sizeof(uint64_t)); d->size = (uint64_t *)calloc(d->nb, sizeof(uint64_t));
     d->crc = (uint32_t *)calloc(d->nb, sizeof(uint32_t)); d->have = (uint8_t *)calloc(d->nb, 1);
@@ -506,6 +542,7 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
         }
         *crc_out = crc; *out_bytes = d->pre[d->nb];
     }
+    if (d->mfd >= 0) close(d->mfd);
     free(d->pre); free(d->size); free(d->crc); free(d->have);
     pthread_mutex_destroy(&d->mu); pthread_cond_destroy(&d->cv);
     pthread_mutex_destroy(&io.mu); pthread_cond_destroy(&io.work); pthread_cond_destroy(&io.done);
@@ -580,8 +617,11 @@ int gzb_zip_fd(int ifd, int ofd, gzb_zip_opts *o)
 
     /* file to file, and more than a small input: no serial stage at all (zip_direct) */
     if (regular && p->out_regular && !o->members && in_left > SMALL && !getenv("GZB_ZIP_NO_DIRECT")) {
-        /* one worker (thread + context) per GPU: its batches overlap inside gzb_internal_deflate_batches */
-        int wpg = 1;
+        /* Workers (thread + context) per GPU.  The batches of one worker overlap inside gzb_internal_deflate_batches, but
+         * read + H2D of a batch take about as long as its kernels, so a lone GPU is only kept busy by three of them (16 GiB
+         * text, tmpfs to tmpfs: 18.1 / 20.0 / 21.4 / 20.9 GB/s with 1 / 2 / 3 / 4 workers; the GPU itself does 21.7).  With
+         * several GPUs the output file is the limit long before (2 GPUs: 30.1 / 25.0 / 24.2 GB/s with 1 / 2 / 3 per GPU). */
+        int wpg = ng == 1 ? 3 : 1;
         { const char *e = getenv("GZB_ZIP_WORKERS_PER_GPU"); if (e && atoi(e) > 0) wpg = atoi(e); }
         if (wpg * ng > MAX_WORKERS) wpg = MAX_WORKERS / ng;
         { const uint64_t nb = (in_left + p->batch - 1) / p->batch; while (wpg > 1 && (uint64_t)(wpg - 1) * (uint64_t)ng >= nb) wpg--; }

@@ -425,7 +425,7 @@ def test_zip_fd_pipeline(gz, orc, tmp_path, monkeypatch):
 def test_zip_fd_file_to_file_variants(gz, orc, ctx, tmp_path, monkeypatch):
     """The file-to-file path of gzb_zip_fd away from its defaults: --rsyncable (16 KiB chunks, no dictionary between
     batches), FNAME / MTIME in the header, an input descriptor that does not stand at the start of its file, more workers
-    than batches, several workers per GPU, a single I/O thread.  Always: header + the one-shot body + trailer."""
+    than batches, several workers per GPU, a single I/O thread, fragments written with pwrite instead of through a mapping.  Always: header + the one-shot body + trailer."""
     n = (41 << 20) + 4321
     d = gz.corpus("mixed", n, seed=77)
     src = tmp_path / "in.bin"; src.write_bytes(b"skip me" * 1000 + d.tobytes())
@@ -445,7 +445,7 @@ def test_zip_fd_file_to_file_variants(gz, orc, ctx, tmp_path, monkeypatch):
     m = run(level=6, name=b"in.bin", mtime=0x01020304)
     assert m[:10] == bytes([31, 139, 8, 8, 4, 3, 2, 1, 0, 3]) and m[10:17] == b"in.bin\0"
     assert m[17:-8] == body6 and m[-8:] == gz.gzip_trailer(crc, n)
-    for env in ({"GZB_ZIP_WORKERS_PER_GPU": "3"}, {"GZB_ZIP_IO_THREADS": "1"}, {"GZB_ZIP_BATCH_MB": "64"}, {"GZB_ZIP_WRITERS": "3", "GZB_ZIP_IO_PIECE_KB": "64"}):
+    for env in ({"GZB_ZIP_WORKERS_PER_GPU": "3"}, {"GZB_ZIP_IO_THREADS": "1"}, {"GZB_ZIP_BATCH_MB": "64"}, {"GZB_ZIP_WRITERS": "3", "GZB_ZIP_IO_PIECE_KB": "64", "GZB_ZIP_NO_MMAP": "1"}, {"GZB_ZIP_NO_MMAP": "1"}):
         for k, v in env.items():
             monkeypatch.setenv(k, v)
         m = run(level=6)
