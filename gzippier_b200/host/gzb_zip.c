@@ -303,12 +303,13 @@ enum { IO_READ = 0, IO_WRITE = 1, IO_COPY = 2 };     /* pread into buf; pwrite f
 typedef struct { int fd, wr; uint8_t *buf, *dst; size_t len; off_t off; io_group *grp; } io_piece;
 typedef struct {
     pthread_mutex_t mu; pthread_cond_t work, done;
-    /* two rings, [0] reads and [1] writes (head: next to take, tail: next free).  Reads run on as many threads as there
-     * are; writes into the one output file exclude each other in the kernel (the inode's lock), so at most max_writers
-     * threads (1) are in a write at a time -- more of them only queue on that lock and slow each other down (measured on
-     * 2 GPUs, 24 CPUs, 16 GiB text: 16.3 GB/s with one writer at a time, 13.7 with two, 13.9 with four). */
-    io_piece q[2][IO_QUEUE]; unsigned head[2], tail[2];
-    int writers, max_writers;
+    /* One ring per kind of piece (head: next to take, tail: next free).  Reads run on as many threads as there are.
+     * pwrite()s into the one output file exclude each other in the kernel (the inode's lock), so at most cap[IO_WRITE] = 1
+     * thread is in one at a time -- more only queue on that lock and slow each other down (2 GPUs, 24 CPUs, 16 GiB text:
+     * 16.3 GB/s with one writer at a time, 13.7 with two, 13.9 with four).  Copies into the output's mapping scale to a
+     * handful of threads and fall off beyond (tools/micro_fallocwrite.c: 7.2 GB/s with 4, 6.0 with 32): cap[IO_COPY] = 6. */
+    io_piece q[3][IO_QUEUE]; unsigned head[3], tail[3];      /* by kind: IO_READ, IO_WRITE, IO_COPY */
+    int busy[3], cap[3];                                      /* threads in a piece of each kind; how many may be */
     int stop, nth; pthread_t th[IO_MAX_THREADS];
 } io_pool;
 
@@ -319,14 +320,16 @@ static void *io_thread(void *arg)
     for (;;) {
         int k;
         for (;;) {
-            if (io->head[1] != io->tail[1] && io->writers < io->max_writers) { k = 1; break; }
-            if (io->head[0] != io->tail[0]) { k = 0; break; }
-            if (io->stop && io->head[1] == io->tail[1]) { k = -1; break; }
+            /* output first (a fragment that waits keeps its pinned buffer), then the reads */
+            if (io->head[IO_WRITE] != io->tail[IO_WRITE] && io->busy[IO_WRITE] < io->cap[IO_WRITE]) { k = IO_WRITE; break; }
+            if (io->head[IO_COPY] != io->tail[IO_COPY] && io->busy[IO_COPY] < io->cap[IO_COPY]) { k = IO_COPY; break; }
+            if (io->head[IO_READ] != io->tail[IO_READ]) { k = IO_READ; break; }
+            if (io->stop && io->head[IO_WRITE] == io->tail[IO_WRITE] && io->head[IO_COPY] == io->tail[IO_COPY]) { k = -1; break; }
             pthread_cond_wait(&io->work, &io->mu);
         }
         if (k < 0) break;
         io_piece pc = io->q[k][io->head[k]++ % IO_QUEUE];
-        io->writers += k;
+        io->busy[k]++;
         pthread_mutex_unlock(&io->mu);
         int rc = 0; size_t done = 0;
         if (pc.wr == IO_COPY) { memcpy(pc.dst, pc.buf, pc.len); done = pc.len; }
@@ -339,7 +342,8 @@ static void *io_thread(void *arg)
         }
         pthread_mutex_lock(&io->mu);
         if (rc) pc.grp->rc = rc;
-        if (k) { io->writers--; if (io->head[1] != io->tail[1]) pthread_cond_signal(&io->work); }   /* a waiting write may go now */
+        io->busy[k]--;
+        if (k != IO_READ && io->head[k] != io->tail[k]) pthread_cond_signal(&io->work);            /* a waiting piece of this kind may go now */
         if (--pc.grp->pending == 0) pthread_cond_broadcast(&io->done);
     }
     pthread_mutex_unlock(&io->mu);
@@ -351,7 +355,7 @@ static void io_submit(io_pool *io, io_group *g, int fd, int wr, uint8_t *buf, si
 {
     pthread_mutex_lock(&io->mu);
     for (size_t o = 0; o < len; o += piece) {
-        const int k = wr == IO_WRITE ? 1 : 0;
+        const int k = wr;
         while (io->tail[k] - io->head[k] == IO_QUEUE) pthread_cond_wait(&io->done, &io->mu);     /* full: never in practice */
         io_piece *pc = &io->q[k][io->tail[k]++ % IO_QUEUE];
         pc->fd = fd; pc->wr = wr; pc->buf = buf + o; pc->dst = dst ? dst + o : NULL; pc->len = len - o < piece ? len - o : piece; pc->off = off + (off_t)o; pc->grp = g;
@@ -377,13 +381,14 @@ typedef struct {
     off_t base, obase;                 /* first input byte; first output byte after the header */
     uint64_t n, batch, dict_sz, out_cap, nb;
     int nw;                            /* workers: batch i belongs to worker i % nw */
-    int mfd, map_off; long pagesz;     /* output reopened read-write for the shared mappings (-1: pwrite only); set when fallocate is not supported */
+    int mfd, map_off; long pagesz;     /* output reopened read-write for the shared mapping (-1: pwrite only); set when fallocate is not supported */
+    uint8_t *map; size_t map_len; off_t map_lo;   /* ONE mapping of everything the fragments can come to, from file offset map_lo on */
     uint64_t known;                    /* batches [0, known) have their sizes in; pre[known] is final */
     uint64_t *pre;                     /* pre[i] = bytes of the fragments before batch i  (nb + 1 entries) */
     uint64_t *size; uint32_t *crc; uint8_t *have;
     gzb_ctx *ctx[MAX_WORKERS];
 } direct_t;
-typedef struct { direct_t *d; int w; io_group rg, wg[2]; void *map[2]; size_t maplen[2]; double t_fetch, t_wait, t_write, t_all; } direct_arg;   /* t_*: seconds, for GZB_ZIP_VERBOSE */
+typedef struct { direct_t *d; int w; io_group rg, wg[2]; double t_fetch, t_wait, t_write, t_all; } direct_arg;   /* t_*: seconds, for GZB_ZIP_VERBOSE */
 
 static void direct_fail(direct_t *d, int rc)
 {
@@ -426,14 +431,11 @@ static int direct_emit(void *user, uint64_t k, const uint8_t *src, const gzb_res
     const uint64_t at = d->pre[i];
     pthread_mutex_unlock(&d->mu);
     if (bad) return GZB_E_IO;
-    /* Writes to one file do not run side by side -- the kernel takes the inode's lock for each (3.8 GB/s into a fresh tmpfs
-     * file on the B200 hosts however many threads write, tools/micro_pwrite.c) -- so the fragment goes as few large pieces,
-     * and the worker does not wait for them: direct_emit_done does, two batches later. */
+    /* The worker does not wait for the fragment's bytes to be in the file: direct_emit_done does, two batches later. */
     direct_arg *a = (direct_arg *)user;
     const off_t lo = d->obase + (off_t)at;
     const size_t len = (size_t)r->out_bytes;
-    a->map[k & 1] = NULL;
-    if (d->mfd >= 0 && len) {
+    if (d->map && !d->map_off && len) {
         /* Reserve, then fill: fallocate() gives the fragment's range its pages (the one serial step, ~15 GB/s; a full file
          * system is an error code HERE, never a SIGBUS later), then the bytes go into a shared mapping of that range from
          * all I/O threads at once -- page-table work instead of the inode's lock (tools/micro_fallocwrite.c: 7 GB/s
@@ -441,18 +443,14 @@ static int direct_emit(void *user, uint64_t k, const uint8_t *src, const gzb_res
         if (fallocate(d->mfd, 0, lo, (off_t)len) != 0) {
             if (errno == EOPNOTSUPP || errno == ENOSYS || errno == EINVAL) { pthread_mutex_lock(&d->mu); d->map_off = 1; pthread_mutex_unlock(&d->mu); }
             else return GZB_E_IO;
-        } else if (!d->map_off) {
-            const off_t pg = lo & ~(off_t)(d->pagesz - 1);
-            const size_t mlen = (size_t)(lo - pg) + len;
-            void *m = mmap(NULL, mlen, PROT_READ | PROT_WRITE, MAP_SHARED, d->mfd, pg);
-            if (m != MAP_FAILED) {
-                a->map[k & 1] = m; a->maplen[k & 1] = mlen;
-                io_submit(d->io, &a->wg[k & 1], -1, IO_COPY, (uint8_t *)(uintptr_t)src, len, 0, IO_PIECE, (uint8_t *)m + (lo - pg));
-                a->t_wait += now_s() - t0;
-                return GZB_OK;
-            }
+        } else {
+            io_submit(d->io, &a->wg[k & 1], -1, IO_COPY, (uint8_t *)(uintptr_t)src, len, 0, IO_PIECE, d->map + (lo - d->map_lo));
+            a->t_wait += now_s() - t0;
+            return GZB_OK;
         }
     }
+    /* pwrite()s into one file do not run side by side (the inode's lock: 3.8 GB/s into a fresh tmpfs file however many
+     * threads write, tools/micro_pwrite.c): few large pieces, one writer at a time */
     io_submit(d->io, &a->wg[k & 1], d->ofd, IO_WRITE, (uint8_t *)(uintptr_t)src, len, lo, (size_t)16 << 20, NULL);
     a->t_wait += now_s() - t0;
     return GZB_OK;
@@ -463,7 +461,6 @@ static int direct_emit_done(void *user, uint64_t k)
     direct_arg *a = (direct_arg *)user;
     const double t0 = now_s();
     const int rc = io_wait(a->d->io, &a->wg[k & 1]) ? GZB_E_IO : GZB_OK;
-    if (a->map[k & 1]) { munmap(a->map[k & 1], a->maplen[k & 1]); a->map[k & 1] = NULL; }
     a->t_write += now_s() - t0;
     return rc;
 }
@@ -500,6 +497,15 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
         char path[64];
         snprintf(path, sizeof(path), "/proc/self/fd/%d", ofd);
         d->mfd = open(path, O_RDWR | O_CLOEXEC);
+        if (d->mfd >= 0) {
+            /* address space only: pages exist where fallocate has put them, and nothing else is ever touched.  One mapping
+             * for the whole call -- mmap / munmap per fragment take the process's mmap lock against every page fault of the
+             * fillers */
+            d->map_lo = obase & ~(off_t)(d->pagesz - 1);
+            d->map_len = (size_t)(obase - d->map_lo) + (size_t)gzb_bound(n, flags) + (size_t)out_cap;
+            void *m = mmap(NULL, d->map_len, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_NORESERVE, d->mfd, d->map_lo);
+            if (m == MAP_FAILED) { close(d->mfd); d->mfd = -1; } else d->map = (uint8_t *)m;
+        }
     }
     for (int w = 0; w < nw; w++) d->ctx[w] = g_pool.ctx[w];
     d->pre = (uint64_t *)calloc(d->nb + 1, sizeof(uint64_t)); d->size = (uint64_t *)calloc(d->nb, sizeof(uint64_t));
@@ -510,8 +516,9 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     int want = ncpu > 0 ? (int)ncpu : 8;
     { const char *e = getenv("GZB_ZIP_IO_THREADS"); if (e && atoi(e) > 0) want = atoi(e); }
-    io.max_writers = 1;
-    { const char *e = getenv("GZB_ZIP_WRITERS"); if (e && atoi(e) > 0) io.max_writers = atoi(e); }
+    io.cap[IO_READ] = IO_MAX_THREADS; io.cap[IO_WRITE] = 1; io.cap[IO_COPY] = 6;
+    { const char *e = getenv("GZB_ZIP_WRITERS"); if (e && atoi(e) > 0) io.cap[IO_WRITE] = atoi(e); }
+    { const char *e = getenv("GZB_ZIP_FILLERS"); if (e && atoi(e) > 0) io.cap[IO_COPY] = atoi(e); }
     { const char *e = getenv("GZB_ZIP_IO_PIECE_KB"); IO_PIECE = (size_t)(e && atoi(e) >= 64 ? atoi(e) : 2048) << 10; }
     if (want > IO_MAX_THREADS) want = IO_MAX_THREADS;
     pthread_t th[MAX_WORKERS]; direct_arg wa[MAX_WORKERS]; int nth = 0;
@@ -542,6 +549,7 @@ static int zip_direct(int ifd, int ofd, gzb_zip_opts *o, uint32_t flags, int nw,
         }
         *crc_out = crc; *out_bytes = d->pre[d->nb];
     }
+    if (d->map) munmap(d->map, d->map_len);
     if (d->mfd >= 0) close(d->mfd);
     free(d->pre); free(d->size); free(d->crc); free(d->have);
     pthread_mutex_destroy(&d->mu); pthread_cond_destroy(&d->cv);

@@ -12,7 +12,7 @@ with open(src, "wb") as f:
     crc = 0
     for off in range(0, n, 1 << 30):
         d = gz.corpus("text", min(1 << 30, n - off), offset=off); f.write(memoryview(d)); crc = zlib.crc32(memoryview(d), crc)
-KNOBS = ["GZB_ZIP_WORKERS_PER_GPU", "GZB_ZIP_IO_THREADS", "GZB_ZIP_IO_PIECE_KB", "GZB_ZIP_BATCH_MB", "GZB_ZIP_NO_DIRECT", "GZB_ZIP_VERBOSE", "GZB_ZIP_WRITERS", "GZB_ZIP_NO_MMAP"]
+KNOBS = ["GZB_ZIP_WORKERS_PER_GPU", "GZB_ZIP_IO_THREADS", "GZB_ZIP_IO_PIECE_KB", "GZB_ZIP_BATCH_MB", "GZB_ZIP_NO_DIRECT", "GZB_ZIP_VERBOSE", "GZB_ZIP_WRITERS", "GZB_ZIP_NO_MMAP", "GZB_ZIP_FILLERS"]
 for g in groups:
     for k in KNOBS: os.environ.pop(k, None)
     for kv in filter(None, g.split(",")):
