@@ -61,3 +61,23 @@ def test_patched_zip_levels_rsyncable_and_sizes(inputs, golden):
             ref = subprocess.run([STOCK, *args, "-j", "4"], stdin=fi, stdout=subprocess.PIPE, check=True).stdout
         assert p.stdout[:10] == ref[:10] and p.stdout[-8:] == ref[-8:]                       # header, CRC32 | ISIZE: byte-equal
         assert len(p.stdout) <= 1.03 * len(ref)
+
+
+def test_reference_boundary_sizes_through_the_patched_zip(gz, inputs, tmp_path):
+    """The size list of the reference's tests/mixed:51-57 (0..64 sampled, 32831-32833, 131071-131073 -- the edges of its
+    window and of a chunk) compressed by the patched binary from a regular file and from a pipe, decoded by the unpatched
+    reference.  Size 0 gives the valid 20-byte member (the reference's own -j path deadlocks there)."""
+    for n in (0, 1, 2, 3, 31, 32, 33, 63, 64, 32831, 32832, 32833, 131071, 131072, 131073):
+        data = gz.corpus("zipf", n, seed=n).tobytes()
+        f = tmp_path / "in"; f.write_bytes(data)
+        with open(f, "rb") as fi:
+            a = subprocess.run([PATCHED, "-6", "-j", "2"], stdin=fi, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert a.returncode == 0, (n, a.stderr)
+        if n in (0, 64, 131073):                                 # every process start is a CUDA context: the pipe variant for three of them
+            b = subprocess.run([PATCHED, "-6"], input=data, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+            assert b.returncode == 0 and a.stdout == b.stdout, (n, b.stderr)
+        if n == 0:
+            assert len(a.stdout) == 20
+        back = subprocess.run([STOCK, "-d"], input=a.stdout, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert back.returncode == 0 and back.stdout == data, n
+
