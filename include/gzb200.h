@@ -172,7 +172,13 @@ int gzb_gzip_trailer(uint32_t crc32, uint64_t isize, uint8_t *out, size_t cap);
  * Mirror of `off_t parallel_zip(int pack_level)` / `off_t deflateGZIP(int)`
  * (src/gzip.h:286,338) with the reference's globals passed explicitly:
  * reads ifd to EOF, writes one gzip member to ofd.  n_gpus devices are used,
- * input sharded by contiguous chunk ranges, no collective. */
+ * input sharded by contiguous chunk ranges, no collective.
+ * Pipes and terminals go through one reader, workers and one in-order writer
+ * (the reference's structure, src/parallel.c:106-143, 490-834).  Between two
+ * regular files nothing is serial: every worker reads its own batches, and a
+ * fragment's range of the output is reserved with fallocate() and filled
+ * through a shared mapping (pwrite where that is not to be had); the input is
+ * taken to end where the file ended when the call began. */
 typedef struct gzb_zip_opts {
     int level;              /* `level`       src/gzip.c:211   */
     int rsyncable;          /* `rsync`       src/gzip.c:244   */
