@@ -453,6 +453,9 @@ def test_zip_fd_file_to_file_variants(gz, orc, ctx, tmp_path, monkeypatch):
         for k in env:
             monkeypatch.delenv(k)
         monkeypatch.setenv("GZB_ZIP_BATCH_MB", "4")
+    for ng in (2, 8):                                       # clamped to the GPUs present; on a multi-GPU box the batches alternate between them
+        m = run(level=6, n_gpus=ng)
+        assert m[10:-8] == body6 and m[-8:] == gz.gzip_trailer(crc, n), ng
     raw, r = ctx.deflate_host(d, 6, gz.F_FINAL | gz.F_RSYNCABLE)
     m = run(level=6, rsyncable=True)
     assert m[10:-8] == raw.tobytes() and zlib.decompress(m, 31) == d.tobytes()
