@@ -512,7 +512,7 @@ def main():
                 "gpu_launches": world * steps * nsub * 5,                    # five kernels per sub-batch of 4096 chunks, on every rank
                 "roofline": {"bound": "hbm", "kernel": top, "achieved": round(achieved, 3), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5),
                              "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                             "note": ("stored chunks: the scan (CRC-32 + byte histogram + gram probe) is the step; traffic is the text capture's" if scan_bound else
+                             "note": ("stored chunks: the scan (CRC-32 + byte histogram + gram probe) is the step; traffic from the committed capture on random bytes" if scan_bound else
                                       "integer/latency-bound path: the HBM fraction is small by construction (SURVEY 8d); see profiles/ for issue-slot utilisation")},
                 "cpu_baseline": cpu, "clocks": res["clocks"]}
         if issue:
